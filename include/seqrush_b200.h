@@ -1,0 +1,177 @@
+/*
+ * seqrush_b200.h -- C ABI of the B200-native align-and-unite hot path of pangenome/seqrush.
+ *
+ * Plain C, plain pointers and sizes; this is what a Rust `extern "C"` block (or cgo / ctypes)
+ * binds. Each entry point cites the reference interface it replaces (paths relative to the
+ * seqrush repository). All functions return 0 on success and a negative SRGPU_E_* code on
+ * failure unless stated otherwise; srgpu_last_error() gives a message for the calling thread.
+ *
+ * Threading: every entry point may be called concurrently from several host threads (the
+ * reference calls BidirectedUnionFind through `&self` from rayon workers, src/seqrush.rs:738-756);
+ * calls on one context are serialised internally.
+ */
+#ifndef SEQRUSH_B200_H_
+#define SEQRUSH_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SRGPU_OK 0
+#define SRGPU_E_CUDA (-1)      /* CUDA runtime error (no device, OOM, launch failure) */
+#define SRGPU_E_ARG (-2)       /* invalid argument (index out of range, bad penalties) */
+#define SRGPU_E_RANGE (-3)     /* Pos outside the union-find (reference: assert in uf_rush lib.rs:113) */
+#define SRGPU_E_VALIDATE (-4)  /* "unite non-matching bases" (reference: panic in validate_match, src/seqrush.rs:1184-1205) */
+#define SRGPU_E_INTERNAL (-5)
+
+/* Per-pair status in srgpu_result.status */
+#define SRGPU_PAIR_OK 0
+#define SRGPU_PAIR_FAILED 1 /* reference: alignment status != Completed -> empty CIGAR, score i32::MAX (allwave/src/alignment.rs:40-55) */
+
+typedef struct srgpu_ctx srgpu_ctx;
+typedef struct srgpu_uf srgpu_uf;
+
+/* Borrowed view of one sequence (reference: allwave::Sequence{id,seq}, allwave/src/types.rs:6-10;
+ * seqrush Sequence{id,data,offset}, src/seqrush.rs:272-277). Offsets in the concatenated Pos
+ * space are the running sum of lengths in array order (src/seqrush.rs:1816-1818). */
+typedef struct {
+  const uint8_t* data;
+  uint64_t len;
+} srgpu_seqview;
+
+/* Reference: allwave::AlignmentParams (allwave/src/types.rs:37-46); match must be 0 and the
+ * two-piece penalties present (AlignmentMode::TwoPieceAffine, types.rs:101-111). */
+typedef struct {
+  int32_t match_score;
+  int32_t mismatch;
+  int32_t gap_open1;
+  int32_t gap_ext1;
+  int32_t gap_open2;
+  int32_t gap_ext2;
+} srgpu_penalties;
+
+/* Reference: allwave::AlignmentResult (allwave/src/types.rs:14-35). CIGAR bytes are in WFA
+ * convention ('M','X','I' = consumes target, 'D' = consumes query), one byte per column, so the
+ * reference's cigar_bytes_to_string (allwave/src/alignment.rs:327-356) applies unchanged. */
+typedef struct {
+  uint32_t query_idx;
+  uint32_t target_idx;
+  int32_t is_reverse;
+  int32_t status;            /* SRGPU_PAIR_* */
+  int32_t score;             /* wf.score(): -penalty when BiWFA split at level 0, INT32_MIN when the
+                                whole pair went through the base case (WFA2-lib quirk), INT32_MAX on failure */
+  int32_t penalty;           /* gap-affine-2p penalty recomputed from the CIGAR (always meaningful) */
+  uint32_t num_matches;      /* count of 'M' */
+  uint32_t alignment_length; /* count of 'M' + 'X' (allwave/src/alignment.rs:279-301) */
+  uint32_t query_end;        /* M + X + D */
+  uint32_t target_end;       /* M + X + I */
+  uint32_t edit_distance;    /* min(fwd, rc) unit-cost distance found by the orientation step */
+  uint32_t n_runs;           /* run-length CIGAR elements */
+  uint64_t cigar_off;        /* offset into the arena returned by srgpu_align_pairs */
+  uint64_t cigar_len;
+  uint64_t wf_cells;         /* wavefront cells computed for this pair (5-component cells) */
+} srgpu_result;
+
+/* Counters and device timings of the last run on a context. */
+typedef struct {
+  uint64_t pairs;
+  uint64_t aligned_bp;     /* sum of query lengths */
+  uint64_t wf_cells;       /* BiWFA cells (one diagonal at one score, 5 components) */
+  uint64_t orient_cells;   /* unit-cost cells of the orientation step */
+  uint64_t unite_ops;      /* BidirectedUnionFind::unite calls issued by unite_matching_region */
+  uint64_t unite_links;    /* unions that actually linked two roots */
+  uint64_t runs;           /* run-length CIGAR elements produced */
+  uint32_t kernel_launches;
+  uint32_t align_launches;
+  uint32_t union_launches;
+  uint32_t retries;
+  float align_ms;          /* CUDA-event time of the align kernel launches */
+  float union_ms;          /* CUDA-event time of the union kernel launches */
+  float total_ms;
+} srgpu_stats;
+
+const char* srgpu_last_error(void);
+
+/* Context: one per GPU. `stream` is a cudaStream_t (NULL = the library creates its own). */
+int srgpu_ctx_create(int device, void* stream, srgpu_ctx** out);
+void srgpu_ctx_destroy(srgpu_ctx* ctx);
+int srgpu_ctx_synchronize(srgpu_ctx* ctx);
+/* Tunables: threads per CTA (multiple of 32), CTAs per SM, initial ring width in diagonals
+ * (0 = automatic). */
+int srgpu_ctx_configure(srgpu_ctx* ctx, int threads, int ctas_per_sm, int ring_diagonals);
+int srgpu_ctx_stats(srgpu_ctx* ctx, srgpu_stats* out);
+
+/* Upload the sequence set (host -> HBM). Replaces the `&[Sequence]` argument of
+ * AllPairIterator::with_options (allwave/src/iterator.rs:30) and SeqRush.sequences. */
+int srgpu_set_sequences(srgpu_ctx* ctx, const srgpu_seqview* seqs, uint32_t n_seqs);
+uint64_t srgpu_total_length(srgpu_ctx* ctx);
+
+/* Batched replacement of AllPairIterator(...).into_par_iter() -> AlignmentResult
+ * (allwave/src/iterator.rs:30-124,185-203 + allwave/src/alignment.rs:16-57): orientation by exact
+ * edit distance, then BiWFA gap-affine-2p, end-to-end, no heuristic. pairs[i] = {query, target}.
+ * On return *cigar_arena (release with srgpu_free) holds all CIGAR bytes; out[i] indexes into it.
+ * cigar_arena may be NULL to skip CIGAR expansion (results only). */
+int srgpu_align_pairs(srgpu_ctx* ctx, const uint32_t (*pairs)[2], uint64_t n_pairs, const srgpu_penalties* pen,
+                      srgpu_result* out, uint8_t** cigar_arena, uint64_t* cigar_arena_len);
+void srgpu_free(void* p);
+
+/* Fused replacement of the closure body src/seqrush.rs:738-756 (align_pair + cigar_bytes_to_string
+ * + process_alignment): align every pair, walk its CIGAR on the device and unite the exact-match
+ * runs of length >= min_match_len into `uf`. out may be NULL. */
+int srgpu_align_and_unite(srgpu_ctx* ctx, srgpu_uf* uf, const uint32_t (*pairs)[2], uint64_t n_pairs,
+                          const srgpu_penalties* pen, uint64_t min_match_len, srgpu_result* out);
+/* Same with the pair list already resident in HBM (device pointer to n_pairs x 2 uint32). */
+int srgpu_align_and_unite_device(srgpu_ctx* ctx, srgpu_uf* uf, const void* d_pairs, uint64_t n_pairs,
+                                 const srgpu_penalties* pen, uint64_t min_match_len);
+
+/* Replacement of process_alignment alone (src/seqrush.rs:1134-1481) for CIGARs that come from
+ * elsewhere (the --paf path, src/seqrush.rs:510-609): cigar is the RLE string ("12=1X3I..."),
+ * 'M' and '=' are re-checked base by base like the reference. */
+int srgpu_process_alignment(srgpu_ctx* ctx, srgpu_uf* uf, const char* cigar, uint32_t query_idx, uint32_t target_idx,
+                            uint64_t min_match_len, int query_is_rc, uint64_t query_start, uint64_t target_start);
+
+/* ---- BidirectedUnionFind (src/bidirected_union_find.rs:7-135) over Pos = offset*2 + is_rev
+ * (src/pos.rs:6-87). HBM-resident parent array, lock-free atomicCAS unions. find() returns the
+ * canonical representative = the minimum Pos of the component (the reference's representative is
+ * schedule-dependent, uf_rush lib.rs:178; only the partition is contractual). ---- */
+int srgpu_uf_new(srgpu_ctx* ctx, uint64_t max_offset, srgpu_uf** out); /* ::new, :16-24: capacity 2*max_offset+2 */
+void srgpu_uf_free(srgpu_uf* uf);
+uint64_t srgpu_uf_capacity(srgpu_uf* uf);
+int srgpu_uf_find(srgpu_uf* uf, uint64_t pos, uint64_t* rep);             /* ::find, :27-31 */
+int srgpu_uf_same(srgpu_uf* uf, uint64_t a, uint64_t b, int* same);       /* ::same, :46-54 */
+int srgpu_uf_unite(srgpu_uf* uf, uint64_t a, uint64_t b);                 /* ::unite, :35-43 */
+int srgpu_uf_unite_matching_region(srgpu_uf* uf, uint64_t seq1_offset, uint64_t seq2_offset, uint64_t seq1_local_start,
+                                   uint64_t seq2_local_start, uint64_t match_length, int seq1_is_rc,
+                                   uint64_t seq1_len); /* :60-98 */
+int srgpu_uf_unite_matching_region_seq2_rc(srgpu_uf* uf, uint64_t seq1_offset, uint64_t seq2_offset,
+                                           uint64_t seq1_local_start, uint64_t seq2_local_start, uint64_t match_length,
+                                           int seq2_is_rc, uint64_t seq2_len); /* :103-129 */
+typedef struct {
+  uint64_t seq1_offset, seq2_offset, seq1_local_start, seq2_local_start, match_length, seq1_len;
+  int32_t seq1_is_rc;
+  int32_t seq2_rc_form; /* 0: unite_matching_region semantics, 1: _seq2_rc semantics (seq1_len = seq2_len) */
+} srgpu_region;
+int srgpu_uf_unite_regions(srgpu_uf* uf, const srgpu_region* regions, uint64_t n);
+/* SeqRush::new's loop `unite(make_pos(i,false), make_pos(i,true))` for i in 0..total_length
+ * (src/seqrush.rs:324-328). */
+int srgpu_uf_unite_fr_all(srgpu_uf* uf, uint64_t total_length);
+/* Bulk find: out[p] = find(p) for p in [first, first+n) (the 2-finds-per-base consumer,
+ * src/bidirected_builder.rs:48-49). */
+int srgpu_uf_roots(srgpu_uf* uf, uint64_t first, uint64_t n, uint64_t* out);
+/* count_components (src/seqrush.rs:341-353): distinct representatives over forward Pos. */
+int srgpu_uf_count_components(srgpu_uf* uf, uint64_t total_length, uint64_t* count);
+/* 64-bit order-independent checksum of the canonical partition (sum over p of mix(p, find(p))). */
+int srgpu_uf_checksum(srgpu_uf* uf, uint64_t* checksum);
+/* Multi-GPU merge (one process per GPU): device pointer + element count of the uint32 parent
+ * array, a compress pass that makes parent[p] == find(p), and a merge pass that unites
+ * (p, roots[p]) for a peer's gathered roots array (device pointer). */
+void* srgpu_uf_device_ptr(srgpu_uf* uf);
+int srgpu_uf_compress(srgpu_uf* uf);
+int srgpu_uf_merge_roots(srgpu_uf* uf, const void* d_peer_roots, uint64_t n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SEQRUSH_B200_H_ */

@@ -1,0 +1,844 @@
+// capi.cu -- host side of the C ABI declared in include/seqrush_b200.h.
+// Owns device memory, the stream, per-CTA workspaces and the chunked launch loop
+// (align kernel -> union kernel per chunk of pairs). There is no CPU fallback: without a CUDA
+// device every entry point fails with SRGPU_E_CUDA.
+#include "../../include/seqrush_b200.h"
+#include "kernels.cuh"
+
+#include <algorithm>
+#include <mutex>
+#include <string>
+#include <vector>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+using namespace srb;
+
+static thread_local std::string g_err;
+extern "C" const char* srgpu_last_error(void) { return g_err.c_str(); }
+
+#define CK(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess) {                                                                       \
+      char buf_[512];                                                                              \
+      snprintf(buf_, sizeof buf_, "%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+      g_err = buf_;                                                                                \
+      return SRGPU_E_CUDA;                                                                         \
+    }                                                                                              \
+  } while (0)
+
+template <class T>
+struct DevBuf {
+  T* p = nullptr;
+  size_t n = 0;
+  int ensure(size_t want) {
+    if (want <= n && p) return 0;
+    if (p) cudaFree(p);
+    p = nullptr;
+    n = 0;
+    if (want == 0) want = 1;
+    cudaError_t e = cudaMalloc((void**)&p, want * sizeof(T));
+    if (e != cudaSuccess) {
+      g_err = std::string("cudaMalloc failed: ") + cudaGetErrorString(e);
+      p = nullptr;
+      return SRGPU_E_CUDA;
+    }
+    n = want;
+    return 0;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    n = 0;
+  }
+};
+
+struct srgpu_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  int n_sm = 148;
+  std::mutex mu;
+  // config
+  int threads = 256;
+  int ctas_per_sm = 4;
+  int ring_diagonals = 0;
+  // sequences
+  uint32_t n_seqs = 0;
+  uint64_t total_len = 0;
+  uint32_t max_len = 0;
+  DevBuf<uint8_t> d_fwd, d_rc, d_rcsafe;
+  DevBuf<uint64_t> d_byte_off, d_pos_off;
+  DevBuf<uint32_t> d_len;
+  std::vector<uint32_t> h_len;
+  std::vector<uint64_t> h_pos_off;
+  // workspaces
+  DevBuf<int32_t> d_ring, d_full, d_orient;
+  DevBuf<WfMeta> d_full_meta;
+  DevBuf<uint32_t> d_runs_tmp, d_bt_tmp;
+  DevBuf<uint2> d_pairs;
+  DevBuf<PairOut> d_out;
+  DevBuf<uint32_t> d_arena, d_todo;
+  DevBuf<unsigned long long> d_scalars;  // [0] arena_head, [1] next_pair(uint) , [4..8] counters
+  DevBuf<unsigned long long> d_byteoff;
+  DevBuf<uint8_t> d_bytes;
+  DevBuf<char> d_cigar_str;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  srgpu_stats stats{};
+};
+
+struct srgpu_uf {
+  srgpu_ctx* ctx = nullptr;
+  uint64_t capacity = 0;
+  DevBuf<uint32_t> parent;
+  DevBuf<unsigned long long> counters;  // [0] ops [1] links [2] validate [3] range
+  DevBuf<RegionDev> regions;
+  DevBuf<uint64_t> tmp64;
+  DevBuf<uint32_t> bitmap;
+};
+
+static inline int grid_for(uint64_t n, int threads, int n_sm) {
+  uint64_t g = (n + threads - 1) / threads;
+  uint64_t cap = (uint64_t)n_sm * 16;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+extern "C" int srgpu_ctx_create(int device, void* stream, srgpu_ctx** out) {
+  if (!out) return SRGPU_E_ARG;
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0) {
+    g_err = std::string("no CUDA device: ") + cudaGetErrorString(e);
+    return SRGPU_E_CUDA;
+  }
+  CK(cudaSetDevice(device));
+  srgpu_ctx* c = new srgpu_ctx();
+  c->device = device;
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, device));
+  c->n_sm = prop.multiProcessorCount;
+  if (stream) {
+    c->stream = (cudaStream_t)stream;
+  } else {
+    CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    c->own_stream = true;
+  }
+  for (int i = 0; i < 4; ++i) CK(cudaEventCreate(&c->ev[i]));
+  *out = c;
+  return SRGPU_OK;
+}
+
+extern "C" void srgpu_ctx_destroy(srgpu_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  c->d_fwd.release(); c->d_rc.release(); c->d_rcsafe.release(); c->d_byte_off.release(); c->d_pos_off.release();
+  c->d_len.release(); c->d_ring.release(); c->d_full.release(); c->d_orient.release(); c->d_full_meta.release();
+  c->d_runs_tmp.release(); c->d_bt_tmp.release(); c->d_pairs.release(); c->d_out.release(); c->d_arena.release();
+  c->d_todo.release(); c->d_scalars.release(); c->d_byteoff.release(); c->d_bytes.release(); c->d_cigar_str.release();
+  for (int i = 0; i < 4; ++i) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+  if (c->own_stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+extern "C" int srgpu_ctx_synchronize(srgpu_ctx* c) {
+  if (!c) return SRGPU_E_ARG;
+  CK(cudaSetDevice(c->device));
+  CK(cudaStreamSynchronize(c->stream));
+  return SRGPU_OK;
+}
+
+extern "C" int srgpu_ctx_configure(srgpu_ctx* c, int threads, int ctas_per_sm, int ring_diagonals) {
+  if (!c) return SRGPU_E_ARG;
+  std::lock_guard<std::mutex> lk(c->mu);
+  if (threads) {
+    if (threads != 128 && threads != 256 && threads != 512) {
+      g_err = "threads must be 128, 256 or 512";
+      return SRGPU_E_ARG;
+    }
+    c->threads = threads;
+  }
+  if (ctas_per_sm > 0) c->ctas_per_sm = ctas_per_sm;
+  if (ring_diagonals >= 0) c->ring_diagonals = ring_diagonals;
+  return SRGPU_OK;
+}
+
+extern "C" int srgpu_ctx_stats(srgpu_ctx* c, srgpu_stats* out) {
+  if (!c || !out) return SRGPU_E_ARG;
+  std::lock_guard<std::mutex> lk(c->mu);
+  *out = c->stats;
+  return SRGPU_OK;
+}
+
+extern "C" uint64_t srgpu_total_length(srgpu_ctx* c) { return c ? c->total_len : 0; }
+
+static const size_t SEQ_PAD = 32;
+
+extern "C" int srgpu_set_sequences(srgpu_ctx* c, const srgpu_seqview* seqs, uint32_t n) {
+  if (!c || (!seqs && n)) return SRGPU_E_ARG;
+  std::lock_guard<std::mutex> lk(c->mu);
+  CK(cudaSetDevice(c->device));
+  std::vector<uint64_t> byte_off(n), pos_off(n);
+  std::vector<uint32_t> len(n);
+  std::vector<uint8_t> rcsafe(n);
+  uint64_t bytes = SEQ_PAD, pos = 0;
+  uint32_t maxlen = 0;
+  for (uint32_t i = 0; i < n; ++i) {
+    if (seqs[i].len == 0) {  // src/seqrush.rs:311-316 panics on empty sequences
+      g_err = "empty sequences are not allowed";
+      return SRGPU_E_ARG;
+    }
+    if (seqs[i].len > 0x3fffffffu) {
+      g_err = "sequence too long for 32-bit wavefront offsets";
+      return SRGPU_E_ARG;
+    }
+    byte_off[i] = bytes;
+    pos_off[i] = pos;
+    len[i] = (uint32_t)seqs[i].len;
+    maxlen = std::max(maxlen, len[i]);
+    bytes += (seqs[i].len + SEQ_PAD + 15) & ~(uint64_t)15;
+    pos += seqs[i].len;
+  }
+  bytes += SEQ_PAD;
+  // pinned staging buffer: padded concatenation
+  uint8_t* stage = nullptr;
+  CK(cudaMallocHost((void**)&stage, bytes));
+  memset(stage, 0, bytes);
+  for (uint32_t i = 0; i < n; ++i) {
+    memcpy(stage + byte_off[i], seqs[i].data, seqs[i].len);
+    uint8_t safe = 1;
+    const uint8_t* d = seqs[i].data;
+    for (uint64_t j = 0; j < seqs[i].len; ++j) {
+      const uint8_t ch = d[j];
+      if (!(ch == 'A' || ch == 'C' || ch == 'G' || ch == 'T' || ch == 'a' || ch == 'c' || ch == 'g' || ch == 't' || ch == 'N')) {
+        safe = 0;
+        break;
+      }
+    }
+    rcsafe[i] = safe;
+  }
+  int rc;
+  if ((rc = c->d_fwd.ensure(bytes)) || (rc = c->d_rc.ensure(bytes)) || (rc = c->d_byte_off.ensure(n)) ||
+      (rc = c->d_pos_off.ensure(n)) || (rc = c->d_len.ensure(n)) || (rc = c->d_rcsafe.ensure(n))) {
+    cudaFreeHost(stage);
+    return rc;
+  }
+  cudaError_t e = cudaMemcpyAsync(c->d_fwd.p, stage, bytes, cudaMemcpyHostToDevice, c->stream);
+  if (e == cudaSuccess) e = cudaMemsetAsync(c->d_rc.p, 0, bytes, c->stream);
+  if (e == cudaSuccess && n) e = cudaMemcpyAsync(c->d_byte_off.p, byte_off.data(), n * 8, cudaMemcpyHostToDevice, c->stream);
+  if (e == cudaSuccess && n) e = cudaMemcpyAsync(c->d_pos_off.p, pos_off.data(), n * 8, cudaMemcpyHostToDevice, c->stream);
+  if (e == cudaSuccess && n) e = cudaMemcpyAsync(c->d_len.p, len.data(), n * 4, cudaMemcpyHostToDevice, c->stream);
+  if (e == cudaSuccess && n) e = cudaMemcpyAsync(c->d_rcsafe.p, rcsafe.data(), n, cudaMemcpyHostToDevice, c->stream);
+  if (e == cudaSuccess && n) {
+    dim3 grid(std::max(1u, std::min(64u, (maxlen + 255) / 256)), std::min(n, 65535u));
+    rc_kernel<<<grid, 256, 0, c->stream>>>(c->d_fwd.p, c->d_rc.p, c->d_byte_off.p, c->d_len.p, n);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+  cudaFreeHost(stage);
+  if (e != cudaSuccess) {
+    g_err = std::string("set_sequences: ") + cudaGetErrorString(e);
+    return SRGPU_E_CUDA;
+  }
+  c->n_seqs = n;
+  c->total_len = pos;
+  c->max_len = maxlen;
+  c->h_len = len;
+  c->h_pos_off = pos_off;
+  return SRGPU_OK;
+}
+
+static SeqTable seq_table(srgpu_ctx* c) {
+  SeqTable t;
+  t.fwd = c->d_fwd.p;
+  t.rc = c->d_rc.p;
+  t.byte_off = c->d_byte_off.p;
+  t.len = c->d_len.p;
+  t.pos_off = c->d_pos_off.p;
+  t.rc_safe = c->d_rcsafe.p;
+  t.n = c->n_seqs;
+  return t;
+}
+
+static int check_penalties(const srgpu_penalties* p, Penalties* out) {
+  if (!p) return SRGPU_E_ARG;
+  if (p->match_score != 0 || p->mismatch <= 0 || p->gap_open1 < 0 || p->gap_ext1 <= 0 || p->gap_open2 < 0 ||
+      p->gap_ext2 <= 0) {
+    g_err = "penalties: need match 0, mismatch > 0, gap_open >= 0, gap_ext > 0 (two-piece affine)";
+    return SRGPU_E_ARG;
+  }
+  out->x = p->mismatch;
+  out->o1 = p->gap_open1;
+  out->e1 = p->gap_ext1;
+  out->o2 = p->gap_open2;
+  out->e2 = p->gap_ext2;
+  out->scope = std::max(std::max(p->gap_open1 + p->gap_ext1, p->gap_open2 + p->gap_ext2), p->mismatch) + 1;
+  if (out->scope > MAX_SCOPE) {
+    g_err = "penalties too large: max_score_scope exceeds the ring depth (64)";
+    return SRGPU_E_ARG;
+  }
+  return 0;
+}
+
+template <int T, int C>
+static cudaError_t launch_align_tc(const AlignArgs& a, int grid, cudaStream_t s) {
+  align_kernel<T, C><<<grid, T, 0, s>>>(a);
+  return cudaGetLastError();
+}
+static cudaError_t launch_align(const AlignArgs& a, int threads, int ctas, int grid, cudaStream_t s) {
+  if (threads == 128) return ctas >= 8 ? launch_align_tc<128, 8>(a, grid, s) : launch_align_tc<128, 4>(a, grid, s);
+  if (threads == 512) return ctas >= 2 ? launch_align_tc<512, 2>(a, grid, s) : launch_align_tc<512, 1>(a, grid, s);
+  if (ctas >= 4) return launch_align_tc<256, 4>(a, grid, s);
+  if (ctas >= 2) return launch_align_tc<256, 2>(a, grid, s);
+  return launch_align_tc<256, 1>(a, grid, s);
+}
+
+// core driver: pairs already on the device (d_pairs). Fills c->d_out (n_pairs records) and, per
+// chunk, runs the union kernel when uf != nullptr. When keep_runs, a single chunk is used and the
+// arena is left intact for CIGAR expansion.
+static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t n_pairs, const Penalties& pen,
+                     uint64_t min_match_len, bool keep_runs) {
+  CK(cudaSetDevice(c->device));
+  c->stats = srgpu_stats{};
+  if (n_pairs == 0) return SRGPU_OK;
+  if (n_pairs > 0xfffffff0ull) {
+    g_err = "too many pairs in one call";
+    return SRGPU_E_ARG;
+  }
+  const uint32_t maxlen = c->max_len;
+  int grid = c->n_sm * c->ctas_per_sm;
+  if ((uint64_t)grid > n_pairs) grid = (int)n_pairs;
+  // workspace geometry
+  const int fullW = (int)(2 * ((uint64_t)maxlen + 4));
+  int W = c->ring_diagonals > 0 ? c->ring_diagonals : 32768;
+  if (W > fullW) W = fullW;
+  W = (W + 63) & ~63;
+  const int cap = std::max(512, 100 * pen.x + 8) + 8;
+  const size_t runs_cap = 2 * (size_t)maxlen + 16;
+  const size_t orient_row = 2 * (size_t)maxlen + 16;
+  int rc;
+  if ((rc = c->d_out.ensure(n_pairs))) return rc;
+  if ((rc = c->d_scalars.ensure(16))) return rc;
+  if ((rc = c->d_full.ensure((size_t)grid * 5 * cap * cap))) return rc;
+  if ((rc = c->d_full_meta.ensure((size_t)grid * cap * 5))) return rc;
+  if ((rc = c->d_orient.ensure((size_t)grid * 4 * orient_row))) return rc;
+  if ((rc = c->d_runs_tmp.ensure((size_t)grid * runs_cap))) return rc;
+  if ((rc = c->d_bt_tmp.ensure((size_t)grid * runs_cap))) return rc;
+  // arena: run-length CIGAR elements of one chunk
+  size_t arena_cap = std::max<size_t>((size_t)64 << 20, 4 * runs_cap);  // 64M runs = 256 MB
+  if (keep_runs) arena_cap = std::max<size_t>(arena_cap, std::min<size_t>((size_t)n_pairs * runs_cap, (size_t)1 << 30));
+  if ((rc = c->d_arena.ensure(arena_cap))) return rc;
+  // chunking: assume <= 1 run per 4 columns on average; overflow is detected and retried
+  uint64_t chunk = keep_runs ? n_pairs : std::max<uint64_t>(1, arena_cap / std::max<size_t>(1, runs_cap / 4));
+  chunk = std::min<uint64_t>(chunk, n_pairs);
+  if (!keep_runs) chunk = std::min<uint64_t>(chunk, std::max<uint64_t>((uint64_t)grid * 8, 4096));
+
+  AlignArgs a;
+  a.seqs = seq_table(c);
+  a.pen = pen;
+  a.full = c->d_full.p;
+  a.full_stride = (size_t)5 * cap * cap;
+  a.full_meta = c->d_full_meta.p;
+  a.cap = cap;
+  a.orient = c->d_orient.p;
+  a.orient_stride = 4 * orient_row;
+  a.orient_row = (int)orient_row;
+  a.runs_tmp = c->d_runs_tmp.p;
+  a.bt_tmp = c->d_bt_tmp.p;
+  a.runs_cap = (uint32_t)runs_cap;
+  a.arena = c->d_arena.p;
+  a.arena_cap = arena_cap;
+  a.arena_head = c->d_scalars.p;
+  a.next_pair = (unsigned int*)(c->d_scalars.p + 1);
+
+  CK(cudaEventRecord(c->ev[0], c->stream));
+  std::vector<PairOut> h_out;
+  std::vector<uint32_t> todo;
+  auto do_union = [&](uint64_t first, const uint32_t* d_todo, uint32_t count) -> int {
+    if (!uf || count == 0) return 0;
+    UnionArgs u;
+    u.seqs = a.seqs;
+    u.out = c->d_out.p + first;
+    u.arena = c->d_arena.p;
+    u.n_pairs = count;
+    u.todo = d_todo;
+    u.parent = uf->parent.p;
+    u.min_match_len = min_match_len;
+    u.counters = uf->counters.p;
+    CK(cudaEventRecord(c->ev[1], c->stream));
+    union_kernel<256><<<std::min<uint32_t>(count, (uint32_t)c->n_sm * 8), 256, 0, c->stream>>>(u);
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(c->ev[2], c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, c->ev[1], c->ev[2]));
+    c->stats.union_ms += ms;
+    c->stats.kernel_launches++;
+    c->stats.union_launches++;
+    return 0;
+  };
+  for (uint64_t first = 0; first < n_pairs; first += chunk) {
+    const uint32_t cn = (uint32_t)std::min<uint64_t>(chunk, n_pairs - first);
+    a.pairs = d_pairs + first;
+    a.out = c->d_out.p + first;
+    a.n_pairs = cn;
+    a.todo = nullptr;
+    int curW = W;
+    int cur_grid = std::min<int>(grid, (int)cn);
+    CK(cudaMemsetAsync(c->d_scalars.p, 0, 2 * sizeof(unsigned long long), c->stream));
+    for (int attempt = 0;; ++attempt) {
+      if ((rc = c->d_ring.ensure((size_t)cur_grid * 2 * pen.scope * 5 * curW))) return rc;
+      a.ring = c->d_ring.p;
+      a.ring_stride = (size_t)2 * pen.scope * 5 * curW;
+      a.W = curW;
+      CK(cudaMemsetAsync(a.next_pair, 0, sizeof(unsigned int), c->stream));
+      CK(cudaEventRecord(c->ev[1], c->stream));
+      cudaError_t e = launch_align(a, c->threads, c->ctas_per_sm, cur_grid, c->stream);
+      if (e != cudaSuccess) {
+        g_err = std::string("align_kernel launch: ") + cudaGetErrorString(e);
+        return SRGPU_E_CUDA;
+      }
+      CK(cudaEventRecord(c->ev[2], c->stream));
+      c->stats.kernel_launches++;
+      c->stats.align_launches++;
+      h_out.resize(cn);
+      CK(cudaMemcpyAsync(h_out.data(), c->d_out.p + first, (size_t)cn * sizeof(PairOut), cudaMemcpyDeviceToHost, c->stream));
+      CK(cudaStreamSynchronize(c->stream));
+      float ms = 0;
+      CK(cudaEventElapsedTime(&ms, c->ev[1], c->ev[2]));
+      c->stats.align_ms += ms;
+      // unite what this launch produced (records of failed pairs are skipped by the kernel)
+      if ((rc = do_union(first, a.todo, a.n_pairs))) return rc;
+      // pairs that need a wider ring or did not fit the arena (rare) are re-run
+      std::vector<uint32_t> again;
+      bool diag = false, arena_over = false;
+      const uint32_t cnt = a.todo ? (uint32_t)todo.size() : cn;
+      for (uint32_t j = 0; j < cnt; ++j) {
+        const uint32_t i = a.todo ? todo[j] : j;
+        const int st = h_out[i].status;
+        if (st == ST_WS_DIAG_OVERFLOW) { again.push_back(i); diag = true; }
+        else if (st == ST_ARENA_OVERFLOW) { again.push_back(i); arena_over = true; }
+      }
+      if (again.empty() || attempt >= 3) break;
+      if (keep_runs && arena_over) {
+        g_err = "CIGAR arena overflow: align fewer pairs per call";
+        return SRGPU_E_INTERNAL;
+      }
+      c->stats.retries++;
+      todo.swap(again);
+      if (diag) curW = (fullW + 63) & ~63;
+      cur_grid = std::min<int>(cur_grid, (int)todo.size());
+      {  // keep the retry ring within ~24 GB
+        const size_t per = (size_t)2 * pen.scope * 5 * curW * sizeof(int32_t);
+        const size_t maxg = std::max<size_t>(1, ((size_t)24 << 30) / per);
+        cur_grid = (int)std::min<size_t>((size_t)cur_grid, maxg);
+      }
+      if ((rc = c->d_todo.ensure(todo.size()))) return rc;
+      CK(cudaMemcpyAsync(c->d_todo.p, todo.data(), todo.size() * 4, cudaMemcpyHostToDevice, c->stream));
+      if (!keep_runs) CK(cudaMemsetAsync(c->d_scalars.p, 0, sizeof(unsigned long long), c->stream));  // arena reuse
+      a.todo = c->d_todo.p;
+      a.n_pairs = (uint32_t)todo.size();
+    }
+    // accumulate stats from the final records of this chunk
+    for (uint32_t i = 0; i < cn; ++i) {
+      c->stats.wf_cells += h_out[i].cells;
+      c->stats.orient_cells += h_out[i].ocells;
+      c->stats.aligned_bp += c->h_len[h_out[i].q];
+      c->stats.runs += h_out[i].n_runs;
+    }
+  }
+  CK(cudaEventRecord(c->ev[3], c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  CK(cudaEventElapsedTime(&c->stats.total_ms, c->ev[0], c->ev[3]));
+  c->stats.pairs = n_pairs;
+  if (uf) {
+    unsigned long long cnt[4];
+    CK(cudaMemcpy(cnt, uf->counters.p, sizeof cnt, cudaMemcpyDeviceToHost));
+    c->stats.unite_ops = cnt[0];
+    c->stats.unite_links = cnt[1];
+  }
+  return SRGPU_OK;
+}
+
+static void fill_result(srgpu_ctx* c, const PairOut& o, srgpu_result* r) {
+  r->query_idx = o.q;
+  r->target_idx = o.t;
+  r->is_reverse = o.is_reverse;
+  const bool ok = (o.status == ST_OK);
+  r->status = ok ? SRGPU_PAIR_OK : SRGPU_PAIR_FAILED;
+  r->score = ok ? o.score : INT32_MAX;
+  r->penalty = ok ? o.penalty : 0;
+  r->num_matches = ok ? o.num_matches : 0;
+  r->alignment_length = ok ? o.num_matches + o.n_mismatch : 0;
+  r->query_end = ok ? o.num_matches + o.n_mismatch + o.n_del : 0;
+  r->target_end = ok ? o.num_matches + o.n_mismatch + o.n_ins : 0;
+  r->edit_distance = o.edit_distance;
+  r->n_runs = o.n_runs;
+  r->cigar_off = 0;
+  r->cigar_len = ok ? (uint64_t)o.num_matches + o.n_mismatch + o.n_ins + o.n_del : 0;
+  r->wf_cells = o.cells;
+  (void)c;
+}
+
+static int upload_pairs(srgpu_ctx* c, const uint32_t (*pairs)[2], uint64_t n_pairs) {
+  for (uint64_t i = 0; i < n_pairs; ++i)
+    if (pairs[i][0] >= c->n_seqs || pairs[i][1] >= c->n_seqs) {
+      g_err = "pair index out of range";
+      return SRGPU_E_ARG;
+    }
+  int rc;
+  if ((rc = c->d_pairs.ensure(n_pairs))) return rc;
+  CK(cudaMemcpyAsync(c->d_pairs.p, pairs, n_pairs * sizeof(uint2), cudaMemcpyHostToDevice, c->stream));
+  return 0;
+}
+
+extern "C" int srgpu_align_pairs(srgpu_ctx* c, const uint32_t (*pairs)[2], uint64_t n_pairs, const srgpu_penalties* pen,
+                                 srgpu_result* out, uint8_t** cigar_arena, uint64_t* cigar_arena_len) {
+  if (!c || (!pairs && n_pairs) || !out) return SRGPU_E_ARG;
+  std::lock_guard<std::mutex> lk(c->mu);
+  CK(cudaSetDevice(c->device));
+  Penalties p;
+  int rc;
+  if ((rc = check_penalties(pen, &p))) return rc;
+  if (cigar_arena) *cigar_arena = nullptr;
+  if (cigar_arena_len) *cigar_arena_len = 0;
+  if (n_pairs == 0) return SRGPU_OK;
+  if ((rc = upload_pairs(c, pairs, n_pairs))) return rc;
+  if ((rc = run_pairs(c, nullptr, c->d_pairs.p, n_pairs, p, 0, cigar_arena != nullptr))) return rc;
+  std::vector<PairOut> h(n_pairs);
+  CK(cudaMemcpy(h.data(), c->d_out.p, n_pairs * sizeof(PairOut), cudaMemcpyDeviceToHost));
+  std::vector<unsigned long long> boff(n_pairs);
+  uint64_t total = 0;
+  for (uint64_t i = 0; i < n_pairs; ++i) {
+    fill_result(c, h[i], &out[i]);
+    out[i].cigar_off = total;
+    boff[i] = total;
+    total += out[i].cigar_len;
+  }
+  if (cigar_arena) {
+    if ((rc = c->d_byteoff.ensure(n_pairs))) return rc;
+    if ((rc = c->d_bytes.ensure(total + 16))) return rc;
+    CK(cudaMemcpyAsync(c->d_byteoff.p, boff.data(), n_pairs * 8, cudaMemcpyHostToDevice, c->stream));
+    expand_kernel<<<(unsigned)std::min<uint64_t>(n_pairs, (uint64_t)c->n_sm * 8), 256, 0, c->stream>>>(
+        c->d_out.p, c->d_arena.p, c->d_byteoff.p, c->d_bytes.p, (uint32_t)n_pairs);
+    CK(cudaGetLastError());
+    c->stats.kernel_launches++;
+    uint8_t* host = (uint8_t*)malloc(total + 1);
+    if (!host) {
+      g_err = "out of host memory for the CIGAR arena";
+      return SRGPU_E_INTERNAL;
+    }
+    CK(cudaMemcpyAsync(host, c->d_bytes.p, total, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    host[total] = 0;
+    *cigar_arena = host;
+    if (cigar_arena_len) *cigar_arena_len = total;
+  }
+  return SRGPU_OK;
+}
+
+extern "C" void srgpu_free(void* p) { free(p); }
+
+static int check_uf(srgpu_ctx* c, srgpu_uf* uf) {
+  if (!uf || uf->ctx != c) {
+    g_err = "union-find handle does not belong to this context";
+    return SRGPU_E_ARG;
+  }
+  if (uf->capacity < 2 * c->total_len) {
+    g_err = "union-find smaller than the sequence set";
+    return SRGPU_E_RANGE;
+  }
+  return 0;
+}
+
+extern "C" int srgpu_align_and_unite(srgpu_ctx* c, srgpu_uf* uf, const uint32_t (*pairs)[2], uint64_t n_pairs,
+                                     const srgpu_penalties* pen, uint64_t min_match_len, srgpu_result* out) {
+  if (!c || (!pairs && n_pairs)) return SRGPU_E_ARG;
+  std::lock_guard<std::mutex> lk(c->mu);
+  CK(cudaSetDevice(c->device));
+  Penalties p;
+  int rc;
+  if ((rc = check_penalties(pen, &p))) return rc;
+  if ((rc = check_uf(c, uf))) return rc;
+  if (n_pairs == 0) return SRGPU_OK;
+  if ((rc = upload_pairs(c, pairs, n_pairs))) return rc;
+  if ((rc = run_pairs(c, uf, c->d_pairs.p, n_pairs, p, min_match_len, false))) return rc;
+  if (out) {
+    std::vector<PairOut> h(n_pairs);
+    CK(cudaMemcpy(h.data(), c->d_out.p, n_pairs * sizeof(PairOut), cudaMemcpyDeviceToHost));
+    for (uint64_t i = 0; i < n_pairs; ++i) fill_result(c, h[i], &out[i]);
+  }
+  return SRGPU_OK;
+}
+
+extern "C" int srgpu_align_and_unite_device(srgpu_ctx* c, srgpu_uf* uf, const void* d_pairs, uint64_t n_pairs,
+                                            const srgpu_penalties* pen, uint64_t min_match_len) {
+  if (!c || (!d_pairs && n_pairs)) return SRGPU_E_ARG;
+  std::lock_guard<std::mutex> lk(c->mu);
+  CK(cudaSetDevice(c->device));
+  Penalties p;
+  int rc;
+  if ((rc = check_penalties(pen, &p))) return rc;
+  if ((rc = check_uf(c, uf))) return rc;
+  return run_pairs(c, uf, (const uint2*)d_pairs, n_pairs, p, min_match_len, false);
+}
+
+extern "C" int srgpu_process_alignment(srgpu_ctx* c, srgpu_uf* uf, const char* cigar, uint32_t qi, uint32_t ti,
+                                       uint64_t min_match_len, int query_is_rc, uint64_t qstart, uint64_t tstart) {
+  if (!c || !cigar) return SRGPU_E_ARG;
+  std::lock_guard<std::mutex> lk(c->mu);
+  CK(cudaSetDevice(c->device));
+  int rc;
+  if ((rc = check_uf(c, uf))) return rc;
+  if (qi >= c->n_seqs || ti >= c->n_seqs) {
+    g_err = "sequence index out of range";
+    return SRGPU_E_ARG;
+  }
+  const size_t n = strlen(cigar);
+  if ((rc = c->d_cigar_str.ensure(n + 1))) return rc;
+  CK(cudaMemcpyAsync(c->d_cigar_str.p, cigar, n, cudaMemcpyHostToDevice, c->stream));
+  process_alignment_kernel<<<1, 32, 0, c->stream>>>(seq_table(c), c->d_cigar_str.p, (uint32_t)n, qi, ti, min_match_len,
+                                                    query_is_rc, qstart, tstart, uf->parent.p, uf->counters.p);
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(c->stream));
+  return SRGPU_OK;
+}
+
+// ---------------------------------------------------------------------------
+// BidirectedUnionFind
+// ---------------------------------------------------------------------------
+extern "C" int srgpu_uf_new(srgpu_ctx* c, uint64_t max_offset, srgpu_uf** out) {
+  if (!c || !out) return SRGPU_E_ARG;
+  std::lock_guard<std::mutex> lk(c->mu);
+  CK(cudaSetDevice(c->device));
+  const uint64_t cap = (max_offset << 1) + 2;  // src/bidirected_union_find.rs:20
+  if (cap > 0xfffffff0ull) {
+    g_err = "union-find capacity exceeds the 32-bit parent array";
+    return SRGPU_E_ARG;
+  }
+  srgpu_uf* u = new srgpu_uf();
+  u->ctx = c;
+  u->capacity = cap;
+  int rc;
+  if ((rc = u->parent.ensure(cap)) || (rc = u->counters.ensure(8))) {
+    delete u;
+    return rc;
+  }
+  uf_init_kernel<<<grid_for(cap, 256, c->n_sm), 256, 0, c->stream>>>(u->parent.p, cap);
+  CK(cudaGetLastError());
+  CK(cudaMemsetAsync(u->counters.p, 0, 8 * sizeof(unsigned long long), c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  *out = u;
+  return SRGPU_OK;
+}
+
+extern "C" void srgpu_uf_free(srgpu_uf* u) {
+  if (!u) return;
+  {
+    std::lock_guard<std::mutex> lk(u->ctx->mu);
+    cudaSetDevice(u->ctx->device);
+    cudaStreamSynchronize(u->ctx->stream);
+    u->parent.release();
+    u->counters.release();
+    u->regions.release();
+    u->tmp64.release();
+    u->bitmap.release();
+  }
+  delete u;
+}
+
+extern "C" uint64_t srgpu_uf_capacity(srgpu_uf* u) { return u ? u->capacity : 0; }
+
+extern "C" int srgpu_uf_roots(srgpu_uf* u, uint64_t first, uint64_t n, uint64_t* out) {
+  if (!u || (!out && n)) return SRGPU_E_ARG;
+  srgpu_ctx* c = u->ctx;
+  std::lock_guard<std::mutex> lk(c->mu);
+  CK(cudaSetDevice(c->device));
+  if (first + n > u->capacity) {
+    g_err = "Pos out of range";
+    return SRGPU_E_RANGE;
+  }
+  if (n == 0) return SRGPU_OK;
+  int rc;
+  if ((rc = u->tmp64.ensure(n))) return rc;
+  uf_roots_kernel<<<grid_for(n, 256, c->n_sm), 256, 0, c->stream>>>(u->parent.p, first, n, u->tmp64.p);
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(out, u->tmp64.p, n * 8, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  return SRGPU_OK;
+}
+
+extern "C" int srgpu_uf_find(srgpu_uf* u, uint64_t pos, uint64_t* rep) {
+  if (!rep) return SRGPU_E_ARG;
+  return srgpu_uf_roots(u, pos, 1, rep);
+}
+
+extern "C" int srgpu_uf_same(srgpu_uf* u, uint64_t a, uint64_t b, int* same) {
+  if (!u || !same) return SRGPU_E_ARG;
+  if (a == b) {  // src/bidirected_union_find.rs:47-49
+    if (a >= u->capacity) {
+      g_err = "Pos out of range";
+      return SRGPU_E_RANGE;
+    }
+    *same = 1;
+    return SRGPU_OK;
+  }
+  uint64_t ra = 0, rb = 0;
+  int rc;
+  if ((rc = srgpu_uf_find(u, a, &ra)) || (rc = srgpu_uf_find(u, b, &rb))) return rc;
+  *same = (ra == rb);
+  return SRGPU_OK;
+}
+
+static int regions_run(srgpu_uf* u, const RegionDev* regs, uint64_t n) {
+  srgpu_ctx* c = u->ctx;
+  std::lock_guard<std::mutex> lk(c->mu);
+  CK(cudaSetDevice(c->device));
+  if (n == 0) return SRGPU_OK;
+  int rc;
+  if ((rc = u->regions.ensure(n))) return rc;
+  unsigned long long before = 0, after = 0;
+  CK(cudaMemcpyAsync(&before, u->counters.p + 3, 8, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemcpyAsync(u->regions.p, regs, n * sizeof(RegionDev), cudaMemcpyHostToDevice, c->stream));
+  uf_regions_kernel<<<(unsigned)std::min<uint64_t>(n, (uint64_t)c->n_sm * 8), 256, 0, c->stream>>>(
+      u->parent.p, u->regions.p, n, u->capacity, u->counters.p);
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(&after, u->counters.p + 3, 8, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  if (after != before) {
+    g_err = "Pos out of range in unite";
+    return SRGPU_E_RANGE;
+  }
+  return SRGPU_OK;
+}
+
+__global__ void uf_unite_raw_kernel(uint32_t* parent, uint32_t a, uint32_t b, unsigned long long* counters) {
+  atomicAdd(&counters[0], 1ull);
+  if (uf_unite(parent, a, b)) atomicAdd(&counters[1], 1ull);
+}
+
+extern "C" int srgpu_uf_unite(srgpu_uf* u, uint64_t a, uint64_t b) {
+  if (!u) return SRGPU_E_ARG;
+  if (a >= u->capacity || b >= u->capacity) {
+    g_err = "Pos out of range";
+    return SRGPU_E_RANGE;
+  }
+  if (a == b) return SRGPU_OK;  // src/bidirected_union_find.rs:40
+  srgpu_ctx* c = u->ctx;
+  std::lock_guard<std::mutex> lk(c->mu);
+  CK(cudaSetDevice(c->device));
+  uf_unite_raw_kernel<<<1, 1, 0, c->stream>>>(u->parent.p, (uint32_t)a, (uint32_t)b, u->counters.p);
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(c->stream));
+  return SRGPU_OK;
+}
+
+extern "C" int srgpu_uf_unite_matching_region(srgpu_uf* u, uint64_t seq1_offset, uint64_t seq2_offset, uint64_t s1,
+                                              uint64_t s2, uint64_t len, int seq1_is_rc, uint64_t seq1_len) {
+  if (!u) return SRGPU_E_ARG;
+  RegionDev r{seq1_offset, seq2_offset, s1, s2, len, seq1_len, seq1_is_rc ? 1 : 0, 0};
+  return regions_run(u, &r, 1);
+}
+extern "C" int srgpu_uf_unite_matching_region_seq2_rc(srgpu_uf* u, uint64_t seq1_offset, uint64_t seq2_offset,
+                                                      uint64_t s1, uint64_t s2, uint64_t len, int seq2_is_rc,
+                                                      uint64_t seq2_len) {
+  if (!u) return SRGPU_E_ARG;
+  RegionDev r{seq1_offset, seq2_offset, s1, s2, len, seq2_len, seq2_is_rc ? 1 : 0, 1};
+  return regions_run(u, &r, 1);
+}
+extern "C" int srgpu_uf_unite_regions(srgpu_uf* u, const srgpu_region* regions, uint64_t n) {
+  if (!u || (!regions && n)) return SRGPU_E_ARG;
+  std::vector<RegionDev> v(n);
+  for (uint64_t i = 0; i < n; ++i) {
+    v[i] = RegionDev{regions[i].seq1_offset, regions[i].seq2_offset, regions[i].seq1_local_start,
+                     regions[i].seq2_local_start, regions[i].match_length, regions[i].seq1_len,
+                     regions[i].seq1_is_rc ? 1 : 0, regions[i].seq2_rc_form ? 1 : 0};
+  }
+  return regions_run(u, v.data(), n);
+}
+
+extern "C" int srgpu_uf_unite_fr_all(srgpu_uf* u, uint64_t total_length) {
+  if (!u) return SRGPU_E_ARG;
+  srgpu_ctx* c = u->ctx;
+  std::lock_guard<std::mutex> lk(c->mu);
+  CK(cudaSetDevice(c->device));
+  if (2 * total_length > u->capacity) {
+    g_err = "Pos out of range";
+    return SRGPU_E_RANGE;
+  }
+  if (!total_length) return SRGPU_OK;
+  uf_unite_fr_kernel<<<grid_for(total_length, 256, c->n_sm), 256, 0, c->stream>>>(u->parent.p, total_length, u->counters.p);
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(c->stream));
+  return SRGPU_OK;
+}
+
+extern "C" int srgpu_uf_count_components(srgpu_uf* u, uint64_t total_length, uint64_t* count) {
+  if (!u || !count) return SRGPU_E_ARG;
+  srgpu_ctx* c = u->ctx;
+  std::lock_guard<std::mutex> lk(c->mu);
+  CK(cudaSetDevice(c->device));
+  if (2 * total_length > u->capacity) {
+    g_err = "Pos out of range";
+    return SRGPU_E_RANGE;
+  }
+  int rc;
+  const size_t words = (u->capacity + 31) / 32;
+  if ((rc = u->bitmap.ensure(words)) || (rc = u->tmp64.ensure(1))) return rc;
+  CK(cudaMemsetAsync(u->bitmap.p, 0, words * 4, c->stream));
+  CK(cudaMemsetAsync(u->tmp64.p, 0, 8, c->stream));
+  if (total_length) {
+    uf_count_kernel<<<grid_for(total_length, 256, c->n_sm), 256, 0, c->stream>>>(u->parent.p, total_length, u->bitmap.p,
+                                                                              (unsigned long long*)u->tmp64.p);
+    CK(cudaGetLastError());
+  }
+  CK(cudaMemcpyAsync(count, u->tmp64.p, 8, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  return SRGPU_OK;
+}
+
+extern "C" int srgpu_uf_checksum(srgpu_uf* u, uint64_t* checksum) {
+  if (!u || !checksum) return SRGPU_E_ARG;
+  srgpu_ctx* c = u->ctx;
+  std::lock_guard<std::mutex> lk(c->mu);
+  CK(cudaSetDevice(c->device));
+  int rc;
+  if ((rc = u->tmp64.ensure(1))) return rc;
+  CK(cudaMemsetAsync(u->tmp64.p, 0, 8, c->stream));
+  uf_checksum_kernel<<<grid_for(u->capacity, 256, c->n_sm), 256, 0, c->stream>>>(u->parent.p, u->capacity,
+                                                                               (unsigned long long*)u->tmp64.p);
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(checksum, u->tmp64.p, 8, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  return SRGPU_OK;
+}
+
+extern "C" void* srgpu_uf_device_ptr(srgpu_uf* u) { return u ? (void*)u->parent.p : nullptr; }
+
+extern "C" int srgpu_uf_compress(srgpu_uf* u) {
+  if (!u) return SRGPU_E_ARG;
+  srgpu_ctx* c = u->ctx;
+  std::lock_guard<std::mutex> lk(c->mu);
+  CK(cudaSetDevice(c->device));
+  uf_compress_kernel<<<grid_for(u->capacity, 256, c->n_sm), 256, 0, c->stream>>>(u->parent.p, u->capacity);
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(c->stream));
+  return SRGPU_OK;
+}
+
+extern "C" int srgpu_uf_merge_roots(srgpu_uf* u, const void* d_peer_roots, uint64_t n) {
+  if (!u || !d_peer_roots) return SRGPU_E_ARG;
+  srgpu_ctx* c = u->ctx;
+  std::lock_guard<std::mutex> lk(c->mu);
+  CK(cudaSetDevice(c->device));
+  if (n > u->capacity) n = u->capacity;
+  uf_merge_kernel<<<grid_for(n, 256, c->n_sm), 256, 0, c->stream>>>(u->parent.p, (const uint32_t*)d_peer_roots, n,
+                                                                   u->counters.p);
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(c->stream));
+  return SRGPU_OK;
+}

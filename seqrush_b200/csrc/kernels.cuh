@@ -1,0 +1,657 @@
+// kernels.cuh -- device kernels of the align-and-unite path (sm_100a).
+//   align_kernel   : persistent CTAs, one pair at a time per CTA: strand choice (orient_core.cuh)
+//                    -> BiWFA gap-affine-2p with on-device backtrace (wfa_core.cuh) -> run-length
+//                    CIGAR copied into the chunk arena.
+//   union_kernel   : one CTA per pair: walks the run-length CIGAR, unites exact-match runs >= k
+//                    in the HBM-resident parent array (atomicCAS link-to-smaller + path halving).
+//   expand_kernel  : run-length CIGAR -> one byte per column ('M','X','I','D').
+//   uf_* kernels   : BidirectedUnionFind entry points (src/bidirected_union_find.rs).
+#pragma once
+#include <cuda_runtime.h>
+#include "orient_core.cuh"
+
+namespace srb {
+
+// ---------------------------------------------------------------------------
+// Union-find on a uint32 parent array. Links always point from the larger root to the smaller
+// one, so parent[x] <= x, cycles are impossible and the final representative of a component is
+// its minimum Pos (the canonical label north_star asks for). find() halves paths with plain
+// stores (an ancestor stays an ancestor forever); roots only change through atomicCAS.
+// Reference semantics: uf_rush lib.rs:112-134 (find), 159-209 (unite) -- partition-equivalent.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t uf_find(uint32_t* __restrict__ parent, uint32_t x) {
+  uint32_t p = parent[x];
+  while (p != x) {
+    const uint32_t gp = parent[p];
+    if (gp != p) parent[x] = gp;
+    x = p;
+    p = gp;
+  }
+  return x;
+}
+// returns true when two roots were linked
+__device__ __forceinline__ bool uf_unite(uint32_t* __restrict__ parent, uint32_t a, uint32_t b) {
+  if (a == b) return false;  // src/bidirected_union_find.rs:40
+  uint32_t ra = uf_find(parent, a), rb = uf_find(parent, b);
+  while (ra != rb) {
+    if (ra < rb) {
+      const uint32_t t = ra;
+      ra = rb;
+      rb = t;
+    }
+    const uint32_t old = atomicCAS(&parent[ra], ra, rb);
+    if (old == ra) return true;
+    ra = uf_find(parent, old);
+    rb = uf_find(parent, rb);
+  }
+  return false;
+}
+
+// ---------------------------------------------------------------------------
+struct SeqTable {
+  const uint8_t* fwd;        // padded concatenation, forward bytes
+  const uint8_t* rc;         // same layout, allwave reverse complement (allwave/src/alignment.rs:174-186)
+  const uint64_t* byte_off;  // start of sequence i inside fwd/rc
+  const uint32_t* len;
+  const uint64_t* pos_off;   // offset in the concatenated Pos space (src/seqrush.rs:1816-1818)
+  const uint8_t* rc_safe;    // 1 when every byte is in ACGTacgtN: allwave RC == seqrush per-base RC
+  uint32_t n;
+};
+
+struct PairOut {  // device-side result record
+  uint32_t q, t;
+  int32_t is_reverse, status, score, penalty;
+  uint32_t num_matches, n_mismatch, n_ins, n_del;
+  uint32_t edit_distance, n_runs;
+  unsigned long long run_off;
+  unsigned long long cells, ocells;
+};
+
+struct AlignArgs {
+  SeqTable seqs;
+  const uint2* pairs;
+  uint32_t n_pairs;
+  Penalties pen;
+  // per-CTA workspace (indexed by blockIdx.x)
+  int32_t* ring;
+  size_t ring_stride;  // ints per CTA = 2*scope*5*W
+  int W;
+  int32_t* full;
+  size_t full_stride;  // ints per CTA = 5*cap*cap
+  WfMeta* full_meta;   // cap*5 per CTA
+  int cap;
+  int32_t* orient;
+  size_t orient_stride;  // ints per CTA = 4*row
+  int orient_row;
+  uint32_t* runs_tmp;
+  uint32_t* bt_tmp;
+  uint32_t runs_cap;  // per CTA
+  // outputs
+  PairOut* out;
+  uint32_t* arena;
+  unsigned long long arena_cap;
+  unsigned long long* arena_head;
+  unsigned int* next_pair;
+  const uint32_t* todo;  // optional indirection (retry lists); nullptr = identity
+};
+
+static constexpr int ST_ARENA_OVERFLOW = 6;
+
+template <int THREADS, int MIN_CTAS>
+__global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
+  __shared__ CtaShared sh;
+  __shared__ unsigned int s_pair;
+  __shared__ unsigned int s_cnt[8];
+  Ctx cx;
+  cx.sh = &sh;
+  cx.tid = threadIdx.x;
+  cx.nt = THREADS;
+  cx.parity = 0;
+  const size_t b = blockIdx.x;
+  PairWorkspace ws;
+  ws.ring_f = a.ring + b * a.ring_stride;
+  ws.ring_r = ws.ring_f + a.ring_stride / 2;
+  ws.W = a.W;
+  ws.full = a.full + b * a.full_stride;
+  ws.full_meta = a.full_meta + b * (size_t)a.cap * 5;
+  ws.cap = a.cap;
+  RunOut ro;
+  ro.runs = a.runs_tmp + b * (size_t)a.runs_cap;
+  ro.cap = a.runs_cap;
+  ro.bt = a.bt_tmp + b * (size_t)a.runs_cap;
+  ro.bt_cap = a.runs_cap;
+  int32_t* obuf = a.orient + b * a.orient_stride;
+  while (true) {
+    __syncthreads();
+    if (threadIdx.x == 0) s_pair = atomicAdd(a.next_pair, 1u);
+    __syncthreads();
+    const unsigned int slot = s_pair;
+    if (slot >= a.n_pairs) break;
+    const unsigned int pi = a.todo ? a.todo[slot] : slot;
+    const uint2 pr = a.pairs[pi];
+    const uint32_t plen = a.seqs.len[pr.x], tlen = a.seqs.len[pr.y];
+    const uint8_t* Pf = a.seqs.fwd + a.seqs.byte_off[pr.x];
+    const uint8_t* Pr = a.seqs.rc + a.seqs.byte_off[pr.x];
+    const uint8_t* T = a.seqs.fwd + a.seqs.byte_off[pr.y];
+    // 1. strand (allwave/src/alignment.rs:24-30)
+    const OrientResult orr = wf_orient(cx, Pf, Pr, T, (int)plen, (int)tlen, obuf, a.orient_row);
+    // 2. BiWFA (allwave/src/alignment.rs:189-276)
+    SeqView sv;
+    sv.p = orr.is_reverse ? Pr : Pf;
+    sv.t = T;
+    const PairResult r = wf_align_pair(cx, sv, (int)plen, (int)tlen, a.pen, ws, ro);
+    // 3. finalize: CIGAR statistics (allwave/src/alignment.rs:279-324), penalty
+    //    (WFA2-lib/alignment/cigar.c:303-343), copy the runs into the chunk arena
+    __syncthreads();
+    if (threadIdx.x < 8) s_cnt[threadIdx.x] = 0;
+    if (threadIdx.x == 0) {
+      unsigned long long off = 0;
+      int st = r.status;
+      if (st == ST_OK) {
+        off = atomicAdd(a.arena_head, (unsigned long long)r.n_runs);
+        if (off + r.n_runs > a.arena_cap) st = ST_ARENA_OVERFLOW;
+      }
+      sh.bcast[3] = st;
+      sh.bcast64[0] = off;
+    }
+    __syncthreads();
+    const int st = sh.bcast[3];
+    const unsigned long long off = sh.bcast64[0];
+    uint32_t c_m = 0, c_x = 0, c_i = 0, c_d = 0, c_pen = 0;
+    if (st == ST_OK) {
+      for (uint32_t i = threadIdx.x; i < r.n_runs; i += THREADS) {
+        const uint32_t run = ro.runs[i];
+        a.arena[off + i] = run;
+        const uint32_t op = run & 3u, len = run >> 2;
+        if (op == OP_M) {
+          c_m += len;
+        } else if (op == OP_X) {
+          c_x += len;
+          c_pen += len * (uint32_t)a.pen.x;
+        } else {
+          if (op == OP_I) c_i += len; else c_d += len;
+          const uint32_t s1 = (uint32_t)a.pen.o1 + (uint32_t)a.pen.e1 * len;
+          const uint32_t s2 = (uint32_t)a.pen.o2 + (uint32_t)a.pen.e2 * len;
+          c_pen += s1 < s2 ? s1 : s2;
+        }
+      }
+      c_m = __reduce_add_sync(0xffffffffu, c_m);
+      c_x = __reduce_add_sync(0xffffffffu, c_x);
+      c_i = __reduce_add_sync(0xffffffffu, c_i);
+      c_d = __reduce_add_sync(0xffffffffu, c_d);
+      c_pen = __reduce_add_sync(0xffffffffu, c_pen);
+      if ((threadIdx.x & 31) == 0) {
+        atomicAdd(&s_cnt[0], c_m);
+        atomicAdd(&s_cnt[1], c_x);
+        atomicAdd(&s_cnt[2], c_i);
+        atomicAdd(&s_cnt[3], c_d);
+        atomicAdd(&s_cnt[4], c_pen);
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      PairOut o;
+      o.q = pr.x;
+      o.t = pr.y;
+      o.is_reverse = orr.is_reverse;
+      o.status = st;
+      o.score = (st == ST_OK) ? r.score : INT32_MAX;
+      o.penalty = (int32_t)s_cnt[4];
+      o.num_matches = s_cnt[0];
+      o.n_mismatch = s_cnt[1];
+      o.n_ins = s_cnt[2];
+      o.n_del = s_cnt[3];
+      o.edit_distance = (uint32_t)orr.distance;
+      o.n_runs = (st == ST_OK) ? r.n_runs : 0;
+      o.run_off = off;
+      o.cells = sh.cells;
+      o.ocells = sh.ocells;
+      a.out[pi] = o;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// allwave reverse complement of every sequence (allwave/src/alignment.rs:174-186)
+// ---------------------------------------------------------------------------
+__global__ void rc_kernel(const uint8_t* __restrict__ fwd, uint8_t* __restrict__ rc, const uint64_t* __restrict__ byte_off,
+                          const uint32_t* __restrict__ len, uint32_t n) {
+  for (uint32_t s = blockIdx.y; s < n; s += gridDim.y) {
+    const uint32_t L = len[s];
+    const uint8_t* src = fwd + byte_off[s];
+    uint8_t* dst = rc + byte_off[s];
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < L; i += gridDim.x * blockDim.x) {
+      const uint8_t c = src[L - 1 - i];
+      uint8_t o = 'N';
+      switch (c) {
+        case 'A': case 'a': o = 'T'; break;
+        case 'T': case 't': o = 'A'; break;
+        case 'C': case 'c': o = 'G'; break;
+        case 'G': case 'g': o = 'C'; break;
+        default: o = 'N'; break;
+      }
+      dst[i] = o;
+    }
+  }
+}
+
+// seqrush's per-base query RC (src/seqrush.rs:1162-1176): unknown bytes are kept
+__device__ __forceinline__ uint8_t seqrush_query_base(const uint8_t* q, uint32_t qlen, uint32_t local_pos, bool rc) {
+  if (!rc) return q[local_pos];
+  const uint8_t c = q[qlen - 1 - local_pos];
+  switch (c) {
+    case 'A': case 'a': return 'T';
+    case 'T': case 't': return 'A';
+    case 'C': case 'c': return 'G';
+    case 'G': case 'g': return 'C';
+    default: return c;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Union kernel: CIGAR walk + unite (src/seqrush.rs:1134-1481 + src/bidirected_union_find.rs:60-98).
+// The run list is canonical, so one 'M' run is exactly one of the reference's match runs (its
+// run accumulator spans consecutive M/= ops, :1214-1218, and is flushed by any other op).
+// Forward pairs and RC pairs whose query is rc_safe need no per-base re-check: WFA 'M' columns
+// compared the very same bytes. Other RC pairs take the serial per-base path.
+// ---------------------------------------------------------------------------
+struct UnionArgs {
+  SeqTable seqs;
+  const PairOut* out;
+  const uint32_t* arena;
+  uint32_t n_pairs;
+  const uint32_t* todo;  // optional indirection (retry lists)
+  uint32_t* parent;
+  unsigned long long min_match_len;
+  unsigned long long* counters;  // [0] unite ops, [1] links, [2] validation failures
+};
+
+static constexpr int UNION_TILE = 1024;
+
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS) union_kernel(UnionArgs a) {
+  __shared__ uint32_t s_qpos[UNION_TILE];   // query position at run start (alignment coordinates)
+  __shared__ uint32_t s_tpos[UNION_TILE];
+  __shared__ uint32_t s_cum[UNION_TILE + 1];  // exclusive prefix of united bases inside the tile
+  __shared__ uint32_t s_scan[3][THREADS];
+  __shared__ uint32_t s_carry[3];
+  unsigned long long ops = 0, links = 0;
+  for (uint32_t slot = blockIdx.x; slot < a.n_pairs; slot += gridDim.x) {
+    const uint32_t pi = a.todo ? a.todo[slot] : slot;
+    const PairOut po = a.out[pi];
+    if (po.status != ST_OK || po.n_runs == 0) continue;
+    if (po.q == po.t && !po.is_reverse) {
+      // self pair aligned forward: every unite(p,p) is skipped by the reference
+      // (src/bidirected_union_find.rs:40); still counted as issued unite calls
+      if (threadIdx.x == 0) {
+        unsigned long long m = 0;
+        for (uint32_t i = 0; i < po.n_runs; ++i) {
+          const uint32_t run = a.arena[po.run_off + i];
+          if ((run & 3u) == OP_M && (run >> 2) >= a.min_match_len) m += run >> 2;
+        }
+        ops += m;
+      }
+      continue;
+    }
+    const uint32_t qlen = a.seqs.len[po.q];
+    const uint64_t qoff = a.seqs.pos_off[po.q], toff = a.seqs.pos_off[po.t];
+    const bool rc = po.is_reverse != 0;
+    if (rc && !a.seqs.rc_safe[po.q]) {
+      // serial exact path with the per-base equality re-check (src/seqrush.rs:1267-1358)
+      if (threadIdx.x == 0) {
+        const uint8_t* q = a.seqs.fwd + a.seqs.byte_off[po.q];
+        const uint8_t* t = a.seqs.fwd + a.seqs.byte_off[po.t];
+        uint32_t p1 = 0, p2 = 0;
+        bool in_run = false;
+        uint32_t rs1 = 0, rs2 = 0, rl = 0;
+        for (uint32_t i = 0; i <= po.n_runs; ++i) {
+          const bool last = (i == po.n_runs);
+          const uint32_t run = last ? 0 : a.arena[po.run_off + i];
+          const uint32_t op = run & 3u, len = run >> 2;
+          if (!last && op == OP_M) {
+            for (uint32_t k = 0; k < len; ++k) {
+              const bool eq = seqrush_query_base(q, qlen, p1 + k, true) == t[p2 + k];
+              if (eq) {
+                if (!in_run) {
+                  in_run = true;
+                  rs1 = p1 + k;
+                  rs2 = p2 + k;
+                  rl = 1;
+                } else {
+                  ++rl;
+                }
+              }
+              if (!eq) {
+                if (in_run && rl >= a.min_match_len) {
+                  for (uint32_t j = 0; j < rl; ++j) {
+                    const uint32_t x = (uint32_t)(2 * (qoff + qlen - 1 - (rs1 + j)) + 1);
+                    const uint32_t y = (uint32_t)(2 * (toff + rs2 + j));
+                    ++ops;
+                    if (uf_unite(a.parent, x, y)) ++links;
+                  }
+                }
+                in_run = false;
+                rl = 0;
+              }
+            }
+            p1 += len;
+            p2 += len;
+          } else {
+            if (in_run && rl >= a.min_match_len) {
+              for (uint32_t j = 0; j < rl; ++j) {
+                const uint32_t x = (uint32_t)(2 * (qoff + qlen - 1 - (rs1 + j)) + 1);
+                const uint32_t y = (uint32_t)(2 * (toff + rs2 + j));
+                ++ops;
+                if (uf_unite(a.parent, x, y)) ++links;
+              }
+            }
+            in_run = false;
+            rl = 0;
+            if (op == OP_X) {
+              p1 += len;
+              p2 += len;
+            } else if (op == OP_D) {
+              p1 += len;  // WFA 'D' consumes the query (allwave/src/alignment.rs:304-319)
+            } else if (op == OP_I) {
+              p2 += len;
+            }
+          }
+        }
+      }
+      continue;
+    }
+    // parallel path
+    __syncthreads();
+    if (threadIdx.x < 3) s_carry[threadIdx.x] = 0;
+    __syncthreads();
+    for (uint32_t tile0 = 0; tile0 < po.n_runs; tile0 += UNION_TILE) {
+      const uint32_t nt = min((uint32_t)UNION_TILE, po.n_runs - tile0);
+      constexpr int PER = UNION_TILE / THREADS;
+      // each thread owns PER consecutive runs
+      uint32_t runs[PER];
+      uint32_t dq = 0, dt = 0, du = 0;
+#pragma unroll
+      for (int j = 0; j < PER; ++j) {
+        const uint32_t i = threadIdx.x * PER + j;
+        const uint32_t run = (i < nt) ? a.arena[po.run_off + tile0 + i] : 0u;
+        runs[j] = run;
+        const uint32_t op = run & 3u, len = run >> 2;
+        if (op == OP_M || op == OP_X) {
+          dq += len;
+          dt += len;
+        } else if (op == OP_D) {
+          dq += len;
+        } else {
+          dt += len;
+        }
+        if (op == OP_M && len >= a.min_match_len) du += len;
+      }
+      s_scan[0][threadIdx.x] = dq;
+      s_scan[1][threadIdx.x] = dt;
+      s_scan[2][threadIdx.x] = du;
+      __syncthreads();
+      // Hillis-Steele inclusive scan over THREADS partials (3 lanes of data)
+      for (int ofs = 1; ofs < THREADS; ofs <<= 1) {
+        uint32_t v0 = 0, v1 = 0, v2 = 0;
+        if ((int)threadIdx.x >= ofs) {
+          v0 = s_scan[0][threadIdx.x - ofs];
+          v1 = s_scan[1][threadIdx.x - ofs];
+          v2 = s_scan[2][threadIdx.x - ofs];
+        }
+        __syncthreads();
+        s_scan[0][threadIdx.x] += v0;
+        s_scan[1][threadIdx.x] += v1;
+        s_scan[2][threadIdx.x] += v2;
+        __syncthreads();
+      }
+      uint32_t q0 = s_carry[0] + s_scan[0][threadIdx.x] - dq;
+      uint32_t t0 = s_carry[1] + s_scan[1][threadIdx.x] - dt;
+      uint32_t u0 = s_scan[2][threadIdx.x] - du;
+      const uint32_t tile_total = s_scan[2][THREADS - 1];
+      const uint32_t tq = s_scan[0][THREADS - 1], tt = s_scan[1][THREADS - 1];
+#pragma unroll
+      for (int j = 0; j < PER; ++j) {
+        const uint32_t i = threadIdx.x * PER + j;
+        const uint32_t run = runs[j];
+        const uint32_t op = run & 3u, len = run >> 2;
+        s_qpos[i] = q0;
+        s_tpos[i] = t0;
+        s_cum[i] = u0;
+        if (op == OP_M || op == OP_X) {
+          q0 += len;
+          t0 += len;
+        } else if (op == OP_D) {
+          q0 += len;
+        } else {
+          t0 += len;
+        }
+        if (op == OP_M && len >= a.min_match_len) u0 += len;
+      }
+      if (threadIdx.x == THREADS - 1) s_cum[UNION_TILE] = tile_total;
+      __syncthreads();
+      // flattened loop over the united bases of this tile: consecutive threads take consecutive
+      // bases, so the parent[] reads of a warp fall into one or two 128-byte lines per side
+      for (uint32_t u = threadIdx.x; u < tile_total; u += THREADS) {
+        // largest i with s_cum[i] <= u (upper_bound - 1)
+        uint32_t lo = 0, hi = UNION_TILE;
+        while (hi - lo > 1) {
+          const uint32_t mid = (lo + hi) >> 1;
+          if (s_cum[mid] <= u) lo = mid; else hi = mid;
+        }
+        const uint32_t within = u - s_cum[lo];
+        const uint32_t p1 = s_qpos[lo] + within, p2 = s_tpos[lo] + within;
+        uint32_t x, y;
+        if (rc) {
+          x = (uint32_t)(2 * (qoff + qlen - 1 - p1) + 1);
+        } else {
+          x = (uint32_t)(2 * (qoff + p1));
+        }
+        y = (uint32_t)(2 * (toff + p2));
+        ++ops;
+        if (uf_unite(a.parent, x, y)) ++links;
+      }
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        s_carry[0] += tq;
+        s_carry[1] += tt;
+      }
+      __syncthreads();
+    }
+  }
+  // counters
+  ops = __reduce_add_sync(0xffffffffu, (unsigned)(ops & 0xffffffffu)) +
+        ((unsigned long long)__reduce_add_sync(0xffffffffu, (unsigned)(ops >> 32)) << 32);
+  links = __reduce_add_sync(0xffffffffu, (unsigned)(links & 0xffffffffu)) +
+          ((unsigned long long)__reduce_add_sync(0xffffffffu, (unsigned)(links >> 32)) << 32);
+  if ((threadIdx.x & 31) == 0) {
+    if (ops) atomicAdd(&a.counters[0], ops);
+    if (links) atomicAdd(&a.counters[1], links);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// run-length CIGAR -> bytes. One CTA per pair; byte_off[pair] precomputed on the host.
+// ---------------------------------------------------------------------------
+__global__ void expand_kernel(const PairOut* __restrict__ out, const uint32_t* __restrict__ arena,
+                              const unsigned long long* __restrict__ byte_off, uint8_t* __restrict__ bytes,
+                              uint32_t n_pairs) {
+  __shared__ unsigned long long s_pos;
+  for (uint32_t pi = blockIdx.x; pi < n_pairs; pi += gridDim.x) {
+    const PairOut po = out[pi];
+    if (po.status != ST_OK) continue;
+    uint8_t* dst = bytes + byte_off[pi];
+    // runs are few (thousands); walk them in order, all threads fill each run
+    unsigned long long pos = 0;
+    for (uint32_t i = 0; i < po.n_runs; ++i) {
+      const uint32_t run = arena[po.run_off + i];
+      const uint32_t len = run >> 2;
+      const uint8_t ch = "MXID"[run & 3u];
+      for (uint32_t j = threadIdx.x; j < len; j += blockDim.x) dst[pos + j] = ch;
+      pos += len;
+    }
+    (void)s_pos;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// BidirectedUnionFind kernels
+// ---------------------------------------------------------------------------
+__global__ void uf_init_kernel(uint32_t* parent, uint64_t n) {
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+    parent[i] = (uint32_t)i;
+}
+__global__ void uf_unite_fr_kernel(uint32_t* parent, uint64_t total_len, unsigned long long* counters) {
+  unsigned long long links = 0;
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < total_len; i += (uint64_t)gridDim.x * blockDim.x)
+    if (uf_unite(parent, (uint32_t)(2 * i), (uint32_t)(2 * i + 1))) ++links;
+  if (links) atomicAdd(&counters[1], links);
+}
+struct RegionDev {
+  unsigned long long seq1_offset, seq2_offset, s1, s2, len, seq1_len;
+  int seq1_is_rc, seq2_rc_form;
+};
+__global__ void uf_regions_kernel(uint32_t* parent, const RegionDev* regs, uint64_t n, uint64_t capacity,
+                                  unsigned long long* counters) {
+  for (uint64_t r = blockIdx.x; r < n; r += gridDim.x) {
+    const RegionDev g = regs[r];
+    for (unsigned long long i = threadIdx.x; i < g.len; i += blockDim.x) {
+      unsigned long long x, y;
+      if (!g.seq2_rc_form) {
+        // src/bidirected_union_find.rs:73-97
+        if (g.seq1_is_rc) {
+          x = 2 * (g.seq1_offset + (g.seq1_len - 1 - (g.s1 + i))) + 1;
+          y = 2 * (g.seq2_offset + g.s2 + i);
+        } else {
+          x = 2 * (g.seq1_offset + g.s1 + i);
+          y = 2 * (g.seq2_offset + g.s2 + i);
+        }
+      } else {
+        // src/bidirected_union_find.rs:113-128
+        x = 2 * (g.seq1_offset + g.s1 + i);
+        if (g.seq1_is_rc) y = 2 * (g.seq2_offset + (g.seq1_len - 1 - (g.s2 + i))) + 1;
+        else y = 2 * (g.seq2_offset + g.s2 + i);
+      }
+      if (x >= capacity || y >= capacity) {
+        atomicAdd(&counters[3], 1ull);
+        continue;
+      }
+      atomicAdd(&counters[0], 1ull);
+      if (uf_unite(parent, (uint32_t)x, (uint32_t)y)) atomicAdd(&counters[1], 1ull);
+    }
+  }
+}
+__global__ void uf_roots_kernel(uint32_t* parent, uint64_t first, uint64_t n, uint64_t* out) {
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+    out[i] = uf_find(parent, (uint32_t)(first + i));
+}
+__global__ void uf_compress_kernel(uint32_t* parent, uint64_t n) {
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    const uint32_t r = uf_find(parent, (uint32_t)i);
+    if (r != (uint32_t)i) parent[i] = r;
+  }
+}
+__global__ void uf_merge_kernel(uint32_t* parent, const uint32_t* peer, uint64_t n, unsigned long long* counters) {
+  unsigned long long links = 0;
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    const uint32_t r = peer[i];
+    if (r != (uint32_t)i && r < n && uf_unite(parent, (uint32_t)i, r)) ++links;
+  }
+  if (links) atomicAdd(&counters[1], links);
+}
+__global__ void uf_count_kernel(uint32_t* parent, uint64_t total_len, uint32_t* bitmap, unsigned long long* count) {
+  // distinct representatives over forward Pos (src/seqrush.rs:341-353): mark each root once
+  unsigned long long c = 0;
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < total_len; i += (uint64_t)gridDim.x * blockDim.x) {
+    const uint32_t r = uf_find(parent, (uint32_t)(2 * i));
+    const uint32_t bit = 1u << (r & 31);
+    if (!(atomicOr(&bitmap[r >> 5], bit) & bit)) ++c;
+  }
+  if (c) atomicAdd(count, c);
+}
+__device__ __forceinline__ unsigned long long mix64(unsigned long long x) {
+  x ^= x >> 33;
+  x *= 0xff51afd7ed558ccdULL;
+  x ^= x >> 33;
+  x *= 0xc4ceb9fe1a85ec53ULL;
+  x ^= x >> 33;
+  return x;
+}
+__global__ void uf_checksum_kernel(uint32_t* parent, uint64_t n, unsigned long long* sum) {
+  unsigned long long c = 0;
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+    c += mix64((i << 32) ^ (unsigned long long)uf_find(parent, (uint32_t)i));
+  if (c) atomicAdd(sum, c);
+}
+
+// generic CIGAR-string walk (the --paf ingestion path shares process_alignment,
+// src/seqrush.rs:510-609): single thread, per-base re-check of 'M'/'=' like :1267-1358.
+__global__ void process_alignment_kernel(SeqTable seqs, const char* cigar, uint32_t cigar_len, uint32_t qi, uint32_t ti,
+                                         unsigned long long min_match_len, int query_is_rc, unsigned long long qstart,
+                                         unsigned long long tstart, uint32_t* parent, unsigned long long* counters) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  const uint8_t* q = seqs.fwd + seqs.byte_off[qi];
+  const uint8_t* t = seqs.fwd + seqs.byte_off[ti];
+  const uint32_t qlen = seqs.len[qi], tlen = seqs.len[ti];
+  const uint64_t qoff = seqs.pos_off[qi], toff = seqs.pos_off[ti];
+  unsigned long long p1 = qstart, p2 = tstart, count = 0;
+  bool in_run = false;
+  unsigned long long rs1 = 0, rs2 = 0, rl = 0;
+  unsigned long long ops = 0, links = 0;
+  auto flush = [&]() {
+    if (in_run && rl >= min_match_len) {
+      for (unsigned long long j = 0; j < rl; ++j) {
+        const uint32_t x = query_is_rc ? (uint32_t)(2 * (qoff + qlen - 1 - (rs1 + j)) + 1) : (uint32_t)(2 * (qoff + rs1 + j));
+        const uint32_t y = (uint32_t)(2 * (toff + rs2 + j));
+        ++ops;
+        if (uf_unite(parent, x, y)) ++links;
+      }
+    }
+    in_run = false;
+    rl = 0;
+  };
+  for (uint32_t ci = 0; ci < cigar_len; ++ci) {
+    const char ch = cigar[ci];
+    if (ch >= '0' && ch <= '9') {
+      count = count * 10 + (unsigned long long)(ch - '0');
+      continue;
+    }
+    if (count == 0) count = 1;
+    if (ch == 'M' || ch == '=') {
+      for (unsigned long long k = 0; k < count; ++k) {
+        if (p1 + k < qlen && p2 + k < tlen) {
+          const bool eq = seqrush_query_base(q, qlen, (uint32_t)(p1 + k), query_is_rc != 0) == t[p2 + k];
+          if (eq) {
+            if (!in_run) {
+              in_run = true;
+              rs1 = p1 + k;
+              rs2 = p2 + k;
+              rl = 1;
+            } else {
+              ++rl;
+            }
+          } else {
+            flush();
+          }
+        }
+      }
+      p1 += count;
+      p2 += count;
+    } else {
+      flush();
+      if (ch == 'X') {
+        p1 += count;
+        p2 += count;
+      } else if (ch == 'I') {
+        p1 += count;  // SAM convention here (after cigar_bytes_to_string's swap): I consumes the query
+      } else if (ch == 'D') {
+        p2 += count;
+      }
+    }
+    count = 0;
+  }
+  flush();
+  atomicAdd(&counters[0], ops);
+  atomicAdd(&counters[1], links);
+}
+
+}  // namespace srb

@@ -142,9 +142,13 @@ struct CtaShared {
   Breakpoint bp;
   int status;
   int bcast[8];
+  unsigned long long bcast64[2];
   // run-length CIGAR assembly
   uint32_t n_runs;
   uint32_t bt_n;
+  // work counters (roofline accounting)
+  unsigned long long cells;   // BiWFA cells: one diagonal at one score, all five components
+  unsigned long long ocells;  // orientation (unit-cost) cells
 };
 
 struct Ctx {
@@ -374,6 +378,7 @@ WFA_FN StepOut wf_step(Ctx& cx, const Dir& d, const Penalties& pen, int s) {
     o.overflow = 1;
     return o;
   }
+  if (cx.tid == 0) cx.sh->cells += (unsigned long long)(hi - lo + 1);
   // output allocation (WFA/wavefront_compute.c:458-505)
   const bool a_i1 = !n_o1 || !n_i1, a_d1 = !n_o1 || !n_d1, a_i2 = !n_o2 || !n_i2, a_d2 = !n_o2 || !n_d2;
   const int32_t* r_mis = st.row(s_mis < 0 ? 0 : s_mis, C_M);
@@ -739,9 +744,13 @@ struct RunOut {
   uint32_t bt_cap;
 };
 
-// thread 0 only
+// thread 0 only; keeps the run list canonical (adjacent runs never share an op)
 WFA_FN bool runs_push(CtaShared* sh, const RunOut& ro, uint32_t op, uint32_t len) {
   if (len == 0) return true;
+  if (sh->n_runs > 0 && (ro.runs[sh->n_runs - 1] & 3u) == op) {
+    ro.runs[sh->n_runs - 1] += (len << 2);
+    return true;
+  }
   if (sh->n_runs >= ro.cap) return false;
   ro.runs[sh->n_runs++] = make_run(op, len);
   return true;
@@ -882,11 +891,17 @@ WFA_FN int wf_base(Ctx& cx, Dir& db, const Penalties& pen, const RunOut& ro) {
   }
   cta_sync();
   if (!cx.sh->bcast[1]) return ST_WS_RUNS_OVERFLOW;
-  // append forward (WFA2-lib/alignment/cigar.c:125-137): reverse the back-to-front runs
-  const uint32_t n = cx.sh->bt_n, base = (uint32_t)cx.sh->bcast[2];
-  for (uint32_t i = cx.tid; i < n; i += cx.nt) ro.runs[base + i] = ro.bt[n - 1 - i];
+  // append forward (WFA2-lib/alignment/cigar.c:125-137): reverse the back-to-front runs; the
+  // first appended run is merged into the previous one when the ops agree (canonical RLE)
+  const uint32_t n = cx.sh->bt_n;
+  uint32_t base = (uint32_t)cx.sh->bcast[2];
+  uint32_t skip = 0;
+  if (n > 0 && base > 0 && ((ro.runs[base - 1] ^ ro.bt[n - 1]) & 3u) == 0) skip = 1;
   cta_sync();
-  if (cx.tid == 0) cx.sh->n_runs = base + n;
+  if (skip && cx.tid == 0) ro.runs[base - 1] += (ro.bt[n - 1] >> 2) << 2;
+  for (uint32_t i = skip + cx.tid; i < n; i += cx.nt) ro.runs[base + i - skip] = ro.bt[n - 1 - i];
+  cta_sync();
+  if (cx.tid == 0) cx.sh->n_runs = base + n - skip;
   return ST_OK;
 }
 
@@ -960,6 +975,7 @@ WFA_FN PairResult wf_align_pair(Ctx& cx, const SeqView& sv, int plen, int tlen, 
   cta_sync();
   if (cx.tid == 0) {
     sh->n_runs = 0;
+    sh->cells = 0;
     sh->sp = 0;
     sh->status = ST_OK;
     Frame f;

@@ -1,0 +1,121 @@
+"""SeqRush pipeline driver for the `--aligner allwave` align-and-unite phase -- host-side mirror of
+src/seqrush.rs (Sequence :272-277, load_sequences :1801-1837, SeqRush::new :308-336,
+align_and_unite_with_allwave :611-757, count_components :341-353). Graph construction, layout and
+GFA output are outside this hot path."""
+import ctypes as C
+from dataclasses import dataclass
+from typing import List, Optional
+
+import numpy as np
+
+from . import _lib
+from .allwave import AlignmentParams, parse_scores
+from .context import Context, default_context
+from .union_find import BidirectedUnionFind
+
+
+@dataclass
+class Sequence:  # src/seqrush.rs:272-277
+    id: str
+    data: bytes
+    offset: int = 0
+
+
+@dataclass
+class Args:  # the subset of src/seqrush.rs:17-152 that reaches the hot path
+    scores: str = "0,5,8,2,24,1"        # -S, :45
+    min_match_length: int = 0           # -k
+    aligner: str = "allwave"
+    sparsification: str = "none"
+    threads: int = 1                    # kept for interface parity; the device schedules pairs itself
+    verbose: bool = False
+
+
+def load_sequences(path: str) -> List[Sequence]:
+    """FASTA reader with the reference's conventions (src/seqrush.rs:1801-1837): id = first word of
+    the header, offset = running sum of lengths, sequence bytes kept as they are (case preserved)."""
+    seqs, cur_id, cur, off = [], None, [], 0
+    with open(path, "rb") as f:
+        for line in f:
+            line = line.rstrip(b"\r\n")
+            if line.startswith(b">"):
+                if cur_id is not None:
+                    data = b"".join(cur)
+                    seqs.append(Sequence(cur_id, data, off))
+                    off += len(data)
+                hdr = line[1:].decode("utf-8", "replace")
+                cur_id = hdr.split()[0] if hdr.split() else ""
+                cur = []
+            elif cur_id is not None:
+                cur.append(line.strip())
+    if cur_id is not None:
+        data = b"".join(cur)
+        seqs.append(Sequence(cur_id, data, off))
+    return seqs
+
+
+class SeqRush:
+    def __init__(self, sequences: List[Sequence], ctx: Optional[Context] = None):  # ::new, :308-336
+        for s in sequences:
+            if len(s.data) == 0:
+                raise ValueError("Empty sequences are not allowed: sequence '%s' has length 0" % s.id)
+        off = 0
+        for s in sequences:  # offsets are the running sum of lengths (:1816-1818)
+            s.offset = off
+            off += len(s.data)
+        self.sequences = sequences
+        self.total_length = off
+        self.ctx = ctx or default_context()
+        self.ctx.set_sequences([s.data for s in sequences])
+        self.union_find = BidirectedUnionFind(self.total_length, self.ctx)
+        self.union_find.unite_fr_all(self.total_length)  # :324-328
+        self.last_results = None
+
+    @classmethod
+    def new(cls, sequences, ctx=None):
+        return cls(sequences, ctx)
+
+    def all_pairs(self) -> np.ndarray:
+        """n^2 ordered pairs including self pairs, i-major (allwave/src/iterator.rs:37-46 with
+        exclude_self=false, src/seqrush.rs:728-735)."""
+        n = len(self.sequences)
+        ii, jj = np.meshgrid(np.arange(n, dtype=np.uint32), np.arange(n, dtype=np.uint32), indexing="ij")
+        return np.ascontiguousarray(np.stack([ii.ravel(), jj.ravel()], axis=1), dtype=np.uint32)
+
+    def align_and_unite(self, args: Args = None, pairs=None, want_results=False):  # :460-508 -> :611-757
+        args = args or Args()
+        if args.aligner != "allwave":
+            raise SystemExit("only --aligner allwave is implemented on the device")  # :504 exits(1)
+        if pairs is None:
+            if args.sparsification not in ("none", "None", None):
+                raise NotImplementedError("sparsified pair lists must be passed explicitly (pairs=...)")
+            pairs = self.all_pairs()
+        pairs = np.ascontiguousarray(np.asarray(pairs, dtype=np.uint32).reshape(-1, 2))
+        pen = parse_scores(args.scores).to_c()
+        n = pairs.shape[0]
+        res = (_lib.Result * n)() if want_results else None
+        _lib.check(_lib.lib().srgpu_align_and_unite(self.ctx._h, self.union_find._h, pairs.ctypes.data, n,
+                                                    C.byref(pen), args.min_match_length, res))
+        self.last_results = res
+        return self.ctx.stats()
+
+    def align_and_unite_device(self, d_pairs_ptr: int, n_pairs: int, args: Args = None):
+        """Same with the pair list already in HBM (used by bench.py's device-resident timing)."""
+        args = args or Args()
+        pen = parse_scores(args.scores).to_c()
+        _lib.check(_lib.lib().srgpu_align_and_unite_device(self.ctx._h, self.union_find._h, d_pairs_ptr, n_pairs,
+                                                           C.byref(pen), args.min_match_length))
+        return self.ctx.stats()
+
+    def process_alignment(self, cigar: str, seq1_idx: int, seq2_idx: int, min_match_len: int, query_is_rc: bool,
+                          query_start: int = 0, target_start: int = 0):  # :1134-1481
+        _lib.check(_lib.lib().srgpu_process_alignment(self.ctx._h, self.union_find._h, cigar.encode(), seq1_idx,
+                                                      seq2_idx, min_match_len, int(bool(query_is_rc)), query_start,
+                                                      target_start))
+
+    def count_components(self) -> int:  # :341-353
+        return self.union_find.count_components(self.total_length)
+
+    def canonical_partition(self) -> np.ndarray:
+        """label[p] = minimum Pos of p's component, for p in 0..2*total_length."""
+        return self.union_find.roots(0, 2 * self.total_length)

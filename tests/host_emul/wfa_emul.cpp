@@ -40,3 +40,19 @@ extern "C" int emul_wfa_align(const char* pattern, int plen, const char* text, i
   delete sh;
   return r.status;
 }
+
+#include "../../seqrush_b200/csrc/orient_core.cuh"
+extern "C" int emul_orient(const char* pf, const char* pr, int plen, const char* text, int tlen, int* dist) {
+  std::vector<uint8_t> a(plen + 64, 0), b(plen + 64, 0), t(tlen + 64, 0);
+  memcpy(a.data() + 32, pf, plen);
+  memcpy(b.data() + 32, pr, plen);
+  memcpy(t.data() + 32, text, tlen);
+  const int stride = plen + tlen + 8;
+  std::vector<int32_t> buf((size_t)4 * stride);
+  CtaShared* sh = new CtaShared();
+  Ctx cx{sh, 0, 1, 0};
+  OrientResult r = wf_orient(cx, a.data() + 32, b.data() + 32, t.data() + 32, plen, tlen, buf.data(), stride);
+  *dist = r.distance;
+  delete sh;
+  return r.is_reverse;
+}
