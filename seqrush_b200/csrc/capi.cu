@@ -63,7 +63,7 @@ struct srgpu_ctx {
   std::mutex mu;
   // config
   int threads = 256;
-  int ctas_per_sm = 4;
+  int ctas_per_sm = 2;
   int ring_diagonals = 0;
   // sequences
   uint32_t n_seqs = 0;
@@ -156,8 +156,8 @@ extern "C" int srgpu_ctx_configure(srgpu_ctx* c, int threads, int ctas_per_sm, i
   if (!c) return SRGPU_E_ARG;
   std::lock_guard<std::mutex> lk(c->mu);
   if (threads) {
-    if (threads != 128 && threads != 256 && threads != 512) {
-      g_err = "threads must be 128, 256 or 512";
+    if (threads != 32 && threads != 64 && threads != 128 && threads != 256 && threads != 512) {
+      g_err = "threads must be 32, 64, 128, 256 or 512";
       return SRGPU_E_ARG;
     }
     c->threads = threads;
@@ -290,6 +290,8 @@ static cudaError_t launch_align_tc(const AlignArgs& a, int grid, cudaStream_t s)
   return cudaGetLastError();
 }
 static cudaError_t launch_align(const AlignArgs& a, int threads, int ctas, int grid, cudaStream_t s) {
+  if (threads == 32) return ctas >= 16 ? launch_align_tc<32, 16>(a, grid, s) : launch_align_tc<32, 8>(a, grid, s);
+  if (threads == 64) return ctas >= 16 ? launch_align_tc<64, 16>(a, grid, s) : launch_align_tc<64, 8>(a, grid, s);
   if (threads == 128) return ctas >= 8 ? launch_align_tc<128, 8>(a, grid, s) : launch_align_tc<128, 4>(a, grid, s);
   if (threads == 512) return ctas >= 2 ? launch_align_tc<512, 2>(a, grid, s) : launch_align_tc<512, 1>(a, grid, s);
   if (ctas >= 4) return launch_align_tc<256, 4>(a, grid, s);
