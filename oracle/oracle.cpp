@@ -128,6 +128,20 @@ extern "C" int orc_align_pair(void* h, const uint8_t* q, int qlen, const uint8_t
   return r.status;
 }
 
+// raw BiWFA call without the orientation step (used to replay WFA2-lib's own golden vectors,
+// WFA2-lib/tests/wfa.utest.check/test.biwfa.affine2p.alg). memory_mode 3 = ultralow (BiWFA), 0 = high.
+extern "C" int orc_wfa_only(void* h, const uint8_t* p, int plen, const uint8_t* t, int tlen, const int* pen5,
+                            int memory_mode, char* cigar_out, int* cigar_len, int* score) {
+  Oracle* o = (Oracle*)h;
+  void* wf = o->wfa_new(pen5[0], pen5[1], pen5[2], pen5[3], pen5[4], memory_mode);
+  const int st = o->wfa_align(wf, (const char*)p, plen, (const char*)t, tlen, cigar_out, cigar_len, score);
+  o->wfa_free(wf);
+  return st;
+}
+extern "C" int orc_edlib(void* h, const uint8_t* q, int qlen, const uint8_t* t, int tlen) {
+  return ((Oracle*)h)->edlib((const char*)q, qlen, (const char*)t, tlen);
+}
+
 // allwave::cigar_bytes_to_string (allwave/src/alignment.rs:327-356): RLE, M->'=', I<->D swapped
 static void cigar_bytes_to_string(const char* b, int n, std::string& out) {
   out.clear();

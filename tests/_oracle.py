@@ -52,6 +52,8 @@ def lib():
     L.orc_open.argtypes = [C.c_char_p]
     L.orc_allwave_rc.argtypes = [vp, u64, vp]
     L.orc_align_pair.argtypes = [vp, vp, i32, vp, i32, C.POINTER(i32), C.c_char_p] + [C.POINTER(i32)] * 5
+    L.orc_wfa_only.argtypes = [vp, vp, i32, vp, i32, vp, i32, C.c_char_p, C.POINTER(i32), C.POINTER(i32)]
+    L.orc_edlib.argtypes = [vp, vp, i32, vp, i32]
     L.orc_cigar_bytes_to_string.argtypes = [C.c_char_p, i32, C.c_char_p, i32]
     L.orc_uf_new.restype = vp
     L.orc_uf_new.argtypes = [u64]
@@ -99,6 +101,19 @@ class Oracle:
                                   C.byref(rev), C.byref(score), C.byref(fe), C.byref(re_))
         return dict(status=st, is_reverse=bool(rev.value), score=score.value, cigar=buf.raw[:n.value],
                     fwd_ed=fe.value, rev_ed=re_.value)
+
+    def wfa_only(self, p, t, pen=(5, 8, 2, 24, 1), memory_mode=3):
+        """Raw WFA2-lib call (pattern, text) without the orientation step: (status, score, cigar bytes)."""
+        p, t = self._arr(p), self._arr(t)
+        buf = C.create_string_buffer(p.size + t.size + 16)
+        n, score = C.c_int(), C.c_int()
+        st = lib().orc_wfa_only(self.h, p.ctypes.data, p.size, t.ctypes.data, t.size, (C.c_int * 5)(*pen), memory_mode,
+                                buf, C.byref(n), C.byref(score))
+        return st, score.value, buf.raw[:n.value]
+
+    def edlib(self, q, t):
+        q, t = self._arr(q), self._arr(t)
+        return lib().orc_edlib(self.h, q.ctypes.data, q.size, t.ctypes.data, t.size)
 
     def run_pairs(self, seqs, pairs, pen=(5, 8, 2, 24, 1), min_match_len=0, threads=1, uf=None, want_results=True):
         """The pair-dispatch loop on CPU threads. Returns (results[n,6] or None, stats dict)."""

@@ -1,0 +1,281 @@
+"""Parity tests proper: the CUDA path, called through the C ABI (seqrush_b200 mirrors -> ctypes ->
+libseqrush_b200.so), against the oracle and the committed goldens. Bit-exact everywhere: strand,
+raw score, CIGAR bytes, unite-call counts, canonical partition."""
+import hashlib
+
+import numpy as np
+import pytest
+
+from conftest import expand_rle, rle
+
+pytestmark = pytest.mark.gpu
+
+INT32_MIN, INT32_MAX = -2**31, 2**31 - 1
+
+
+@pytest.fixture(scope="module")
+def s(built):
+    import torch
+    assert torch.cuda.is_available(), "gpu tests need a CUDA device"
+    import seqrush_b200 as s
+    return s
+
+
+def _align(s, seq_bytes, pairs, params=None):
+    it = s.AllPairIterator([s.AllwaveSequence("s%d" % i, b) for i, b in enumerate(seq_bytes)],
+                           params or s.AlignmentParams(), False, False, pairs=pairs, ctx=s.Context(0))
+    res = it.align_all()
+    it.ctx.close()
+    return res
+
+
+def test_wfa2_goldens_through_abi(s, wfa2_golden, oracle):
+    """The reference's 305 BiWFA gap-affine-2p vectors (penalties 0,4,6,2,24,1). The ABI always runs the
+    strand step first, so vectors whose reverse complement is closer are checked against the oracle's
+    align_pair instead of the forward golden line."""
+    vec = wfa2_golden["vectors"]
+    seqs, pairs = [], []
+    for v in vec:
+        seqs += [v["p"].encode(), v["t"].encode()]
+        pairs.append((len(seqs) - 2, len(seqs) - 1))
+    pen = wfa2_golden["penalties"]
+    res = _align(s, seqs, pairs, s.AlignmentParams(*pen))
+    n_fwd = 0
+    for v, r in zip(vec, res):
+        o = oracle.align_pair(v["p"].encode(), v["t"].encode(), pen=tuple(pen[1:]))
+        assert r.is_reverse == o["is_reverse"]
+        assert r.cigar_bytes == o["cigar"] and r.score == o["score"]
+        if not r.is_reverse:
+            assert rle(r.cigar_bytes) == v["cigar"] and -r.penalty == v["score"]
+            n_fwd += 1
+    assert n_fwd >= 290
+
+
+def test_seqrush_pairs_goldens(s, seqrush_golden):
+    cases = seqrush_golden["cases"]
+    seqs, pairs = [], []
+    for c in cases:
+        seqs += [c["q"].encode("latin1"), c["t"].encode("latin1")]
+        pairs.append((len(seqs) - 2, len(seqs) - 1))
+    res = _align(s, seqs, pairs)
+    for c, r in zip(cases, res):
+        assert int(r.is_reverse) == c["is_reverse"], c["tag"]
+        assert r.edit_distance == min(c["fwd_ed"], c["rev_ed"]), c["tag"]
+        assert r.score == c["score"], c["tag"]
+        assert rle(r.cigar_bytes) == c["cigar"], c["tag"]
+        cig = r.cigar_bytes
+        assert r.num_matches == cig.count(b"M") and r.alignment_length == cig.count(b"M") + cig.count(b"X")
+        assert r.query_end == len(c["q"]) and r.target_end == len(c["t"])  # end-to-end: consumes both fully
+
+
+def test_config1_hla_drb1_full(s, c1_golden, oracle):
+    """BASELINE.json configs[0]: 144 ordered pairs of HLA-zoo DRB1-3123 (944 N bytes, 22 RC pairs, 30
+    INT32_MIN scores), -k 0 and -k 11: strand, score, CIGAR digest, unite calls, canonical partition."""
+    exp, ids, seqs = c1_golden
+    n = len(seqs)
+    pairs = [(i, j) for i in range(n) for j in range(n)]
+    res = _align(s, seqs, pairs)
+    for e, r in zip(exp["pairs"], res):
+        assert (r.query_idx, r.target_idx) == (e["q"], e["t"])
+        assert int(r.is_reverse) == e["is_reverse"] and r.score == e["score"]
+        assert r.edit_distance == min(e["fwd_ed"], e["rev_ed"])
+        assert len(r.cigar_bytes) == e["cigar_len"]
+        assert hashlib.sha1(r.cigar_bytes).hexdigest() == e["cigar_sha1"], (e["q"], e["t"])
+    for part in exp["partitions"]:
+        ctx = s.Context(0)
+        sr = s.SeqRush([s.Sequence(i, d) for i, d in zip(ids, seqs)], ctx=ctx)
+        st = sr.align_and_unite(s.Args(min_match_length=part["min_match_len"]))
+        assert st["unite_ops"] == part["unite_calls"]
+        canon = sr.canonical_partition()
+        assert hashlib.sha1(canon.astype("<u8").tobytes()).hexdigest() == part["partition_sha1"]
+        assert sr.count_components() == part["components"]
+        ctx.close()
+
+
+@pytest.mark.parametrize("cfg", [(8, 6000, 0.01, 11, 0.0, 0.0), (10, 4000, 0.03, 12, 0.3, 0.3), (5, 15000, 0.02, 13, 0.2, 0.0)])
+def test_seeded_sets_vs_oracle(s, oracle, cfg):
+    """Seeded synthetic sets (incl. RC sequences + inversions): every ordered pair and the partition."""
+    import _oracle
+    from seqrush_b200 import synth
+    ids, seqs = synth.make_sequences(*cfg)
+    ctx = s.Context(0)
+    sr = s.SeqRush([s.Sequence(i, a.tobytes()) for i, a in zip(ids, seqs)], ctx=ctx)
+    pairs = sr.all_pairs()
+    res = _align(s, [a.tobytes() for a in seqs], pairs)
+    ores, _ = oracle.run_pairs(seqs, pairs, threads=4)
+    for k, r in enumerate(res):
+        o = oracle.align_pair(seqs[r.query_idx], seqs[r.target_idx]) if k % 7 == 0 else None
+        assert int(r.is_reverse) == ores[k][0] and r.score == ores[k][2] and len(r.cigar_bytes) == ores[k][3]
+        if o is not None:
+            assert r.cigar_bytes == o["cigar"]
+    for k in (0, 16):
+        sr.union_find.close()
+        sr.union_find = s.BidirectedUnionFind(sr.total_length, ctx)
+        sr.union_find.unite_fr_all(sr.total_length)
+        st = sr.align_and_unite(s.Args(min_match_length=k))
+        ouf = _oracle.OracleUF(sr.total_length)
+        ouf.unite_fr_all(sr.total_length)
+        _, ost = oracle.run_pairs(seqs, pairs, min_match_len=k, threads=4, uf=ouf, want_results=False)
+        assert st["unite_ops"] == ost["unite_calls"]
+        assert np.array_equal(sr.canonical_partition(), ouf.canonical(2 * sr.total_length))
+        assert sr.count_components() == ouf.count_components(sr.total_length)
+    ctx.close()
+
+
+def test_ragged_and_degenerate_inputs(s, oracle):
+    seqs = [b"A", b"C", b"ACGT" * 30, b"ACGT" * 30 + b"TT", b"G" * 150, b"ACGTNNNNacgtRYKM" * 9, b"T" * 7]
+    pairs = [(i, j) for i in range(len(seqs)) for j in range(len(seqs))]
+    res = _align(s, seqs, pairs)
+    for r in res:
+        o = oracle.align_pair(seqs[r.query_idx], seqs[r.target_idx])
+        assert (r.is_reverse, r.score, r.cigar_bytes) == (o["is_reverse"], o["score"], o["cigar"]), (r.query_idx, r.target_idx)
+    assert _align(s, seqs, np.zeros((0, 2), dtype=np.uint32)) == []
+
+
+def test_error_behaviour(s):
+    ctx = s.Context(0)
+    with pytest.raises(s.SrgpuError) as e:
+        ctx.set_sequences([b"ACGT", b""])  # src/seqrush.rs:311-316 panics on empty sequences
+    assert e.value.code == -2
+    with pytest.raises(ValueError):
+        s.SeqRush([s.Sequence("a", b"")], ctx=ctx)
+    it = s.AllPairIterator([s.AllwaveSequence("a", b"ACGT")], s.AlignmentParams(), False, False, pairs=[(0, 3)], ctx=ctx)
+    with pytest.raises(s.SrgpuError) as e:
+        it.align_all()
+    assert e.value.code == -2
+    uf = s.BidirectedUnionFind(10, ctx)
+    with pytest.raises(s.SrgpuError) as e:
+        uf.unite(3, 22)  # uf_rush asserts x < size (lib.rs:113)
+    assert e.value.code == -3
+    with pytest.raises(s.SrgpuError):
+        uf.find(22)
+    with pytest.raises(s.SrgpuError):
+        s.AllPairIterator([s.AllwaveSequence("a", b"ACGT")], s.AlignmentParams(1, 5, 8, 2, 24, 1), False, False,
+                          pairs=[(0, 0)], ctx=ctx).align_all()
+    ctx.close()
+
+
+def test_union_find_kats(s):
+    """src/bidirected_union_find.rs:137-257, tests/test_graph_construction.rs:98-139."""
+    ctx = s.Context(0)
+    uf = s.BidirectedUnionFind.new(1000, ctx)
+    assert uf.capacity == 2002
+    assert not uf.same(220, 430) and uf.same(7, 7)
+    uf.unite_matching_region(100, 200, 10, 15, 5, False, 100)
+    assert uf.same(110 * 2, 215 * 2) and uf.same(114 * 2, 219 * 2) and not uf.same(115 * 2, 220 * 2)
+    uf2 = s.BidirectedUnionFind(1000, ctx)
+    uf2.unite_matching_region(100, 200, 10, 15, 3, True, 50)
+    assert uf2.same(139 * 2 + 1, 215 * 2) and uf2.same(137 * 2 + 1, 217 * 2)
+    assert not uf2.same(139 * 2, 215 * 2)      # no implicit forward/reverse unite on a bare union-find
+    uf3 = s.BidirectedUnionFind(1000, ctx)
+    uf3.unite_matching_region_seq2_rc(100, 200, 10, 15, 3, True, 50)
+    assert uf3.same(110 * 2, (200 + 50 - 1 - 15) * 2 + 1) and uf3.same(112 * 2, (200 + 50 - 1 - 17) * 2 + 1)
+    # transitivity + canonical representative = min Pos
+    uf.unite(2, 40)
+    uf.unite(40, 600)
+    assert uf.same(2, 600) and uf.find(600) == 2 and uf.find(40) == 2
+    uf.unite(9, 9)
+    assert uf.find(9) == 9
+    uf.unite_fr_all(500)
+    assert uf.same(4, 5) and uf.count_components(500) <= 500
+    ctx.close()
+
+
+def test_uf_concurrent_stress(s):
+    """uf_rush lib.rs:330-374 in spirit: many concurrent unites -> exactly one component, and the batched
+    region form equals the sequential oracle."""
+    import _oracle
+    ctx = s.Context(0)
+    n = 200_000
+    uf = s.BidirectedUnionFind(n, ctx)
+    rng = np.random.default_rng(3)
+    regs, ouf = [], _oracle.OracleUF(n)
+    for _ in range(400):
+        ln = int(rng.integers(1, 3000))
+        a, b = int(rng.integers(0, n - ln)), int(rng.integers(0, n - ln))
+        rc = bool(rng.integers(0, 2))
+        regs.append((a, 0, 0, b, ln, True, ln) if rc else (0, 0, a, b, ln, False, ln))
+        o1, o2, s1, s2, l, r, l1 = regs[-1]
+        ouf.unite_matching_region(o1, o2, s1, s2, l, r, l1)
+    uf.unite_regions(regs)
+    assert np.array_equal(uf.roots(0, uf.capacity), ouf.canonical(uf.capacity))
+    chain = s.BidirectedUnionFind(n, ctx)
+    chain.unite_regions([(0, 0, 0, 1, n - 1, False, 0)])  # unite(2i, 2i+2) for all i at once
+    roots = chain.roots(0, 2 * n)
+    assert (roots[0::2] == 0).all() and (roots[1::2] == np.arange(1, 2 * n, 2)).all()
+    ctx.close()
+
+
+def test_process_alignment_paf_path(s, oracle):
+    """src/seqrush.rs:510-609 shares process_alignment: 'M' ops hiding mismatches, RC query, starts."""
+    import _oracle
+    q = b"ACGTACGTACGGTTACAGGATTACA"
+    t = b"ACGTTCGTACGGTTACAGCATTACA"
+    for cigar, k, rc, qs, ts in (("25M", 0, False, 0, 0), ("25M", 6, False, 0, 0), ("4=1X20=", 0, False, 0, 0),
+                                 ("10M2I3M2D8M", 0, False, 0, 0), ("20M", 3, True, 2, 3), ("5=1X5=", 0, True, 0, 0)):
+        ctx = s.Context(0)
+        sr = s.SeqRush([s.Sequence("q", q), s.Sequence("t", t)], ctx=ctx)
+        sr.union_find.close()
+        sr.union_find = s.BidirectedUnionFind(sr.total_length, ctx)
+        sr.process_alignment(cigar, 0, 1, k, rc, qs, ts)
+        ouf = _oracle.OracleUF(len(q) + len(t))
+        ouf.process_alignment(cigar, q, 0, t, len(q), k, rc, qs, ts)
+        assert np.array_equal(sr.union_find.roots(0, 2 * sr.total_length), ouf.canonical(2 * sr.total_length)), cigar
+        ctx.close()
+
+
+def test_properties_at_bench_scale(s):
+    """Size-independent properties on a slice of BASELINE.json configs[1] (100 x 50 kb, 1 %): the
+    partition does not depend on pair order or launch configuration, re-running is idempotent, CIGARs
+    consume both sequences, and the raw score equals minus the penalty recomputed from the CIGAR."""
+    from seqrush_b200 import synth
+    ids, seqs = synth.make_config("c2", n=12)
+    ctx = s.Context(0)
+    sr = s.SeqRush([s.Sequence(i, a.tobytes()) for i, a in zip(ids, seqs)], ctx=ctx)
+    pairs = sr.all_pairs()
+    st = sr.align_and_unite(s.Args(min_match_length=0), want_results=True)
+    res = sr.last_results
+    for i in range(len(pairs)):
+        r = res[i]
+        assert r.status == 0 and r.query_end == seqs[r.query_idx].size and r.target_end == seqs[r.target_idx].size
+        assert r.score in (-r.penalty, INT32_MIN)
+        if r.query_idx != r.target_idx:
+            assert r.score == -r.penalty and 1000 < r.penalty < 12000
+    ck = sr.union_find.checksum()
+    comps = sr.count_components()
+    sr.align_and_unite(s.Args(min_match_length=0))        # idempotent
+    assert sr.union_find.checksum() == ck
+    ctx2 = s.Context(0)
+    ctx2.configure(threads=64, ctas_per_sm=8, ring_diagonals=4096)   # narrow ring: exercises the retry path
+    sr2 = s.SeqRush([s.Sequence(i, a.tobytes()) for i, a in zip(ids, seqs)], ctx=ctx2)
+    perm = np.random.default_rng(0).permutation(len(pairs))
+    st2 = sr2.align_and_unite(s.Args(min_match_length=0), pairs=pairs[perm])
+    assert sr2.union_find.checksum() == ck and sr2.count_components() == comps
+    assert st2["unite_ops"] == st["unite_ops"] and st2["wf_cells"] == st["wf_cells"]
+    assert st2["retries"] >= 1
+    ctx.close()
+    ctx2.close()
+
+
+def test_forest_merge_on_device(s):
+    """Multi-GPU merge path on one device: two private forests over disjoint pair shards, merged through
+    compress + merge_roots, equal the single forest (the N>1 collective only moves the arrays)."""
+    from seqrush_b200 import synth
+    from seqrush_b200.distributed import shard_pairs
+    ids, seqs = synth.make_sequences(6, 5000, 0.02, 21, 0.3, 0.0)
+    ctx = s.Context(0)
+    mk = lambda: s.SeqRush([s.Sequence(i, a.tobytes()) for i, a in zip(ids, seqs)], ctx=ctx)
+    whole = mk()
+    pairs = whole.all_pairs()
+    whole.align_and_unite(pairs=pairs)
+    a, b = mk(), mk()
+    a.align_and_unite(pairs=shard_pairs(pairs, 0, 2))
+    b.align_and_unite(pairs=shard_pairs(pairs, 1, 2))
+    a.union_find.compress()
+    b.union_find.compress()
+    a.union_find.merge_roots(b.union_find.device_ptr(), b.union_find.capacity)
+    a.union_find.compress()
+    assert np.array_equal(a.canonical_partition(), whole.canonical_partition())
+    t = a.union_find.as_tensor()
+    assert t.is_cuda and t.numel() == a.union_find.capacity
+    ctx.close()

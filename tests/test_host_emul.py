@@ -1,0 +1,61 @@
+"""Control logic of the CUDA aligner (seqrush_b200/csrc/wfa_core.cuh, orient_core.cuh) compiled for
+the host with a one-thread "CTA" (tests/host_emul) and checked against the goldens. This is a
+CPU-side logic test only; the product library never contains the host build."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, expand_rle, rle
+
+
+@pytest.fixture(scope="module")
+def emul(built):
+    L = C.CDLL(os.path.join(ROOT, "tests", "host_emul", "libwfa_emul.so"))
+    L.emul_wfa_align.argtypes = [C.c_char_p, C.c_int, C.c_char_p, C.c_int] + [C.c_int] * 7 + [C.c_char_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.emul_orient.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, C.c_int, C.POINTER(C.c_int)]
+    return L
+
+
+def _align(L, p, t, pen, W=0, cap=0):
+    W = W or 2 * (max(len(p), len(t)) + 8)
+    W = (W + 63) & ~63
+    cap = cap or max(512, 100 * pen[0] + 8) + 8
+    buf = C.create_string_buffer(len(p) + len(t) + 16)
+    n, sc = C.c_int(), C.c_int()
+    st = L.emul_wfa_align(p, len(p), t, len(t), *pen, W, cap, buf, C.byref(n), C.byref(sc))
+    return st, sc.value, buf.raw[:n.value]
+
+
+def test_emul_wfa2_goldens(emul, wfa2_golden):
+    pen = tuple(wfa2_golden["penalties"][1:])
+    for i, v in enumerate(wfa2_golden["vectors"]):
+        st, score, cig = _align(emul, v["p"].encode(), v["t"].encode(), pen)
+        assert st == 0 and rle(cig) == v["cigar"], i
+
+
+def test_emul_seqrush_pairs(emul, seqrush_golden):
+    from seqrush_b200.allwave import reverse_complement
+    n = 0
+    for c in seqrush_golden["cases"]:
+        q, t = c["q"].encode("latin1"), c["t"].encode("latin1")
+        if max(len(q), len(t)) > 8100:
+            continue
+        rc = reverse_complement(q)
+        d = C.c_int()
+        is_rev = emul.emul_orient(q, rc, len(q), t, len(t), C.byref(d))
+        assert is_rev == c["is_reverse"], c["tag"]
+        assert d.value == min(c["fwd_ed"], c["rev_ed"]), c["tag"]
+        st, score, cig = _align(emul, rc if is_rev else q, t, (5, 8, 2, 24, 1))
+        assert st == 0 and score == c["score"] and rle(cig) == c["cigar"], c["tag"]
+        n += 1
+    assert n >= 40
+
+
+def test_emul_narrow_ring_reports_overflow(emul):
+    rng = np.random.default_rng(1)
+    a = bytes(np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, 3000)])
+    b = bytes(np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, 3000)])
+    st, _, _ = _align(emul, a, b, (5, 8, 2, 24, 1), W=256)
+    assert st == 2  # ST_WS_DIAG_OVERFLOW: the host retries with a wider ring, never a wrong answer

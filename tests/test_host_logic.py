@@ -1,0 +1,69 @@
+"""Host-side mirror of the reference interfaces (no device needed)."""
+import numpy as np
+import pytest
+
+import seqrush_b200 as s
+from seqrush_b200 import pos
+from seqrush_b200.distributed import shard_pairs
+
+
+def test_pos_roundtrip():
+    """src/pos.rs:89-160."""
+    p = pos.make_pos(42, False)
+    assert pos.offset(p) == 42 and not pos.is_rev(p) and pos.orientation_char(p) == "+"
+    r = pos.make_pos(42, True)
+    assert pos.offset(r) == 42 and pos.is_rev(r) and pos.orientation_char(r) == "-"
+    assert pos.flip_orientation(p) == r and pos.flip_orientation(r) == p
+    assert pos.incr_pos(p) == pos.make_pos(43, False) and pos.decr_pos(p) == pos.make_pos(41, False)
+    assert pos.incr_pos(r) == pos.make_pos(41, True) and pos.decr_pos(r) == pos.make_pos(43, True)
+    assert pos.incr_pos(pos.make_pos(0, True)) == pos.make_pos(0, True)
+    assert pos.decr_pos(pos.make_pos(0, False)) == pos.make_pos(0, False)
+    assert [pos.rc_base(b) for b in b"ACGTNacgtX"] == list(b"TGCANTGCAX")
+
+
+def test_allwave_helpers():
+    assert s.reverse_complement(b"ACGTNacgtRY") == b"NNACGTNACGT"  # allwave/src/alignment.rs:174-186
+    assert s.cigar_bytes_to_string(b"MMMMXIIDMM") == "4=1X2D1I2="
+    assert s.cigar_bytes_to_string(b"") == ""
+    p = s.parse_scores("0,5,8,2,24,1")
+    assert (p.match_score, p.mismatch_penalty, p.gap_open, p.gap_extend, p.gap2_open, p.gap2_extend) == (0, 5, 8, 2, 24, 1)
+    assert s.parse_scores("0,5,8,2").gap2_open is None
+    with pytest.raises(ValueError):
+        s.parse_scores("1,2,3")
+    with pytest.raises(ValueError):
+        s.parse_scores("0,5,8,2").to_c()
+
+
+def test_paf_line():
+    """allwave/src/lib.rs:71-112."""
+    seqs = [s.AllwaveSequence("q", b"ACGTACGT"), s.AllwaveSequence("t", b"ACGTTCGT")]
+    r = s.AlignmentResult(0, 1, 0, 8, 0, 8, False, b"MMMMXMMM", -5, 7, 8)
+    f = s.alignment_to_paf(r, seqs).split("\t")
+    assert f[:9] == ["q", "8", "0", "8", "+", "t", "8", "0", "8"] and f[9:12] == ["7", "8", "60"]
+    assert f[12] == "cg:Z:4=1X3="
+
+
+def test_load_sequences(tmp_path):
+    """src/seqrush.rs:1801-1837: id = first word, offsets = running sum, case preserved."""
+    fa = tmp_path / "x.fa"
+    fa.write_text(">s1 desc here\nACGT\nacgt\n>s2\nNNNN\n")
+    seqs = s.load_sequences(str(fa))
+    assert [(q.id, q.data, q.offset) for q in seqs] == [("s1", b"ACGTacgt", 0), ("s2", b"NNNN", 8)]
+
+
+def test_pair_order_and_sharding():
+    """allwave/src/iterator.rs:37-46: i-major ordered pairs, self pairs kept when exclude_self=false."""
+    from bench import all_pairs
+    pr = all_pairs(3)
+    assert pr.tolist() == [[0, 0], [0, 1], [0, 2], [1, 0], [1, 1], [1, 2], [2, 0], [2, 1], [2, 2]]
+    parts = [shard_pairs(pr, r, 2) for r in range(2)]
+    assert sorted(map(tuple, np.concatenate(parts).tolist())) == sorted(map(tuple, pr.tolist()))
+    assert abs(parts[0].shape[0] - parts[1].shape[0]) <= 1
+
+
+def test_synth_is_deterministic():
+    from seqrush_b200 import synth
+    a = synth.make_config("c2", n=3, length=2000)[1]
+    b = synth.make_config("c2", n=3, length=2000)[1]
+    assert all(np.array_equal(x, y) for x, y in zip(a, b))
+    assert all(set(np.unique(x).tolist()) <= set(b"ACGT") for x in a)
