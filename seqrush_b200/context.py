@@ -1,5 +1,6 @@
 """Device context: one per GPU (owns the stream, the uploaded sequence set and the workspaces)."""
 import ctypes as C
+import weakref
 
 import numpy as np
 
@@ -15,11 +16,20 @@ class Context:
         _lib.check(_lib.lib().srgpu_ctx_create(device, C.c_void_p(stream or None), C.byref(self._h)))
         self._seq_keep = None
         self.n_seqs = 0
+        self._children = weakref.WeakSet()  # union-finds living on this context: freed before it
 
     def close(self):
+        for ch in list(getattr(self, "_children", ())):
+            ch.close()
         if getattr(self, "_h", None) and self._h.value:
             _lib.lib().srgpu_ctx_destroy(self._h)
             self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
     def configure(self, threads=0, ctas_per_sm=0, ring_diagonals=-1):
         _lib.check(_lib.lib().srgpu_ctx_configure(self._h, threads, ctas_per_sm, ring_diagonals))

@@ -29,6 +29,14 @@ extern "C" const char* srgpu_last_error(void) { return g_err.c_str(); }
     }                                                                                              \
   } while (0)
 
+#define UF_ALIVE(u)                                                        \
+  do {                                                                     \
+    if (!(u)->ctx) {                                                       \
+      g_err = "union-find handle outlived its context (already destroyed)"; \
+      return SRGPU_E_ARG;                                                  \
+    }                                                                      \
+  } while (0)
+
 template <class T>
 struct DevBuf {
   T* p = nullptr;
@@ -87,7 +95,9 @@ struct srgpu_ctx {
   DevBuf<char> d_cigar_str;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   srgpu_stats stats{};
+  std::vector<srgpu_uf*> ufs;  // union-finds living on this context (orphaned when it is destroyed)
 };
+static std::mutex g_registry_mu;
 
 struct srgpu_uf {
   srgpu_ctx* ctx = nullptr;
@@ -98,6 +108,16 @@ struct srgpu_uf {
   DevBuf<uint64_t> tmp64;
   DevBuf<uint32_t> bitmap;
 };
+
+static void orphan_uf(srgpu_uf* u) {
+  u->parent.release();
+  u->counters.release();
+  u->regions.release();
+  u->tmp64.release();
+  u->bitmap.release();
+  u->ctx = nullptr;
+  u->capacity = 0;
+}
 
 static inline int grid_for(uint64_t n, int threads, int n_sm) {
   uint64_t g = (n + threads - 1) / threads;
@@ -136,6 +156,11 @@ extern "C" void srgpu_ctx_destroy(srgpu_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
+  {  // a union-find that outlives its context keeps a valid handle but no device memory
+    std::lock_guard<std::mutex> lk(g_registry_mu);
+    for (srgpu_uf* u : c->ufs) orphan_uf(u);
+    c->ufs.clear();
+  }
   c->d_fwd.release(); c->d_rc.release(); c->d_rcsafe.release(); c->d_byte_off.release(); c->d_pos_off.release();
   c->d_len.release(); c->d_ring.release(); c->d_full.release(); c->d_orient.release(); c->d_full_meta.release();
   c->d_runs_tmp.release(); c->d_bt_tmp.release(); c->d_pairs.release(); c->d_out.release(); c->d_arena.release();
@@ -634,21 +659,27 @@ extern "C" int srgpu_uf_new(srgpu_ctx* c, uint64_t max_offset, srgpu_uf** out) {
   CK(cudaGetLastError());
   CK(cudaMemsetAsync(u->counters.p, 0, 8 * sizeof(unsigned long long), c->stream));
   CK(cudaStreamSynchronize(c->stream));
+  {
+    std::lock_guard<std::mutex> rk(g_registry_mu);
+    c->ufs.push_back(u);
+  }
   *out = u;
   return SRGPU_OK;
 }
 
 extern "C" void srgpu_uf_free(srgpu_uf* u) {
   if (!u) return;
+  srgpu_ctx* c;
   {
-    std::lock_guard<std::mutex> lk(u->ctx->mu);
-    cudaSetDevice(u->ctx->device);
-    cudaStreamSynchronize(u->ctx->stream);
-    u->parent.release();
-    u->counters.release();
-    u->regions.release();
-    u->tmp64.release();
-    u->bitmap.release();
+    std::lock_guard<std::mutex> rk(g_registry_mu);
+    c = u->ctx;
+    if (c) c->ufs.erase(std::remove(c->ufs.begin(), c->ufs.end(), u), c->ufs.end());
+  }
+  if (c) {
+    std::lock_guard<std::mutex> lk(c->mu);
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    orphan_uf(u);
   }
   delete u;
 }
@@ -657,6 +688,7 @@ extern "C" uint64_t srgpu_uf_capacity(srgpu_uf* u) { return u ? u->capacity : 0;
 
 extern "C" int srgpu_uf_roots(srgpu_uf* u, uint64_t first, uint64_t n, uint64_t* out) {
   if (!u || (!out && n)) return SRGPU_E_ARG;
+  UF_ALIVE(u);
   srgpu_ctx* c = u->ctx;
   std::lock_guard<std::mutex> lk(c->mu);
   CK(cudaSetDevice(c->device));
@@ -681,6 +713,7 @@ extern "C" int srgpu_uf_find(srgpu_uf* u, uint64_t pos, uint64_t* rep) {
 
 extern "C" int srgpu_uf_same(srgpu_uf* u, uint64_t a, uint64_t b, int* same) {
   if (!u || !same) return SRGPU_E_ARG;
+  UF_ALIVE(u);
   if (a == b) {  // src/bidirected_union_find.rs:47-49
     if (a >= u->capacity) {
       g_err = "Pos out of range";
@@ -697,6 +730,7 @@ extern "C" int srgpu_uf_same(srgpu_uf* u, uint64_t a, uint64_t b, int* same) {
 }
 
 static int regions_run(srgpu_uf* u, const RegionDev* regs, uint64_t n) {
+  UF_ALIVE(u);
   srgpu_ctx* c = u->ctx;
   std::lock_guard<std::mutex> lk(c->mu);
   CK(cudaSetDevice(c->device));
@@ -725,6 +759,7 @@ __global__ void uf_unite_raw_kernel(uint32_t* parent, uint32_t a, uint32_t b, un
 
 extern "C" int srgpu_uf_unite(srgpu_uf* u, uint64_t a, uint64_t b) {
   if (!u) return SRGPU_E_ARG;
+  UF_ALIVE(u);
   if (a >= u->capacity || b >= u->capacity) {
     g_err = "Pos out of range";
     return SRGPU_E_RANGE;
@@ -765,6 +800,7 @@ extern "C" int srgpu_uf_unite_regions(srgpu_uf* u, const srgpu_region* regions, 
 
 extern "C" int srgpu_uf_unite_fr_all(srgpu_uf* u, uint64_t total_length) {
   if (!u) return SRGPU_E_ARG;
+  UF_ALIVE(u);
   srgpu_ctx* c = u->ctx;
   std::lock_guard<std::mutex> lk(c->mu);
   CK(cudaSetDevice(c->device));
@@ -781,6 +817,7 @@ extern "C" int srgpu_uf_unite_fr_all(srgpu_uf* u, uint64_t total_length) {
 
 extern "C" int srgpu_uf_count_components(srgpu_uf* u, uint64_t total_length, uint64_t* count) {
   if (!u || !count) return SRGPU_E_ARG;
+  UF_ALIVE(u);
   srgpu_ctx* c = u->ctx;
   std::lock_guard<std::mutex> lk(c->mu);
   CK(cudaSetDevice(c->device));
@@ -805,6 +842,7 @@ extern "C" int srgpu_uf_count_components(srgpu_uf* u, uint64_t total_length, uin
 
 extern "C" int srgpu_uf_checksum(srgpu_uf* u, uint64_t* checksum) {
   if (!u || !checksum) return SRGPU_E_ARG;
+  UF_ALIVE(u);
   srgpu_ctx* c = u->ctx;
   std::lock_guard<std::mutex> lk(c->mu);
   CK(cudaSetDevice(c->device));
@@ -823,6 +861,7 @@ extern "C" void* srgpu_uf_device_ptr(srgpu_uf* u) { return u ? (void*)u->parent.
 
 extern "C" int srgpu_uf_compress(srgpu_uf* u) {
   if (!u) return SRGPU_E_ARG;
+  UF_ALIVE(u);
   srgpu_ctx* c = u->ctx;
   std::lock_guard<std::mutex> lk(c->mu);
   CK(cudaSetDevice(c->device));
@@ -834,6 +873,7 @@ extern "C" int srgpu_uf_compress(srgpu_uf* u) {
 
 extern "C" int srgpu_uf_merge_roots(srgpu_uf* u, const void* d_peer_roots, uint64_t n) {
   if (!u || !d_peer_roots) return SRGPU_E_ARG;
+  UF_ALIVE(u);
   srgpu_ctx* c = u->ctx;
   std::lock_guard<std::mutex> lk(c->mu);
   CK(cudaSetDevice(c->device));

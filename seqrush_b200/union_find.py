@@ -15,6 +15,7 @@ class BidirectedUnionFind:
         self._h = C.c_void_p()
         _lib.check(_lib.lib().srgpu_uf_new(self.ctx._h, max_offset, C.byref(self._h)))
         self.capacity = _lib.lib().srgpu_uf_capacity(self._h)
+        self.ctx._children.add(self)
 
     @classmethod
     def new(cls, max_offset: int, ctx=None):
