@@ -70,15 +70,19 @@ struct srgpu_ctx {
   int n_sm = 148;
   std::mutex mu;
   // config
-  int threads = 256;
-  int ctas_per_sm = 2;
+  int threads = 128;
+  int ctas_per_sm = 8;
   int ring_diagonals = 0;
   // sequences
   uint32_t n_seqs = 0;
   uint64_t total_len = 0;
   uint32_t max_len = 0;
-  DevBuf<uint8_t> d_fwd, d_rc, d_rcsafe;
-  DevBuf<uint64_t> d_byte_off, d_pos_off;
+  DevBuf<uint8_t> d_fwd, d_rcsafe;
+  DevBuf<uint64_t> d_byte_off, d_pos_off, d_pk_off;
+  DevBuf<uint32_t> d_pk_fwd, d_pk_rc;
+  int lbits = 3;              // log2(bits per packed symbol): 1, 2 or 3
+  uint32_t max_pk_words = 0;  // packed words of the longest sequence incl. guards
+  int smem_budget = 96 * 1024;  // dynamic shared memory the align kernel may use for staged sequences
   DevBuf<uint32_t> d_len;
   std::vector<uint32_t> h_len;
   std::vector<uint64_t> h_pos_off;
@@ -161,7 +165,7 @@ extern "C" void srgpu_ctx_destroy(srgpu_ctx* c) {
     for (srgpu_uf* u : c->ufs) orphan_uf(u);
     c->ufs.clear();
   }
-  c->d_fwd.release(); c->d_rc.release(); c->d_rcsafe.release(); c->d_byte_off.release(); c->d_pos_off.release();
+  c->d_fwd.release(); c->d_pk_fwd.release(); c->d_pk_rc.release(); c->d_pk_off.release(); c->d_rcsafe.release(); c->d_byte_off.release(); c->d_pos_off.release();
   c->d_len.release(); c->d_ring.release(); c->d_full.release(); c->d_orient.release(); c->d_full_meta.release();
   c->d_runs_tmp.release(); c->d_bt_tmp.release(); c->d_pairs.release(); c->d_out.release(); c->d_arena.release();
   c->d_todo.release(); c->d_scalars.release(); c->d_byteoff.release(); c->d_bytes.release(); c->d_cigar_str.release();
@@ -181,8 +185,8 @@ extern "C" int srgpu_ctx_configure(srgpu_ctx* c, int threads, int ctas_per_sm, i
   if (!c) return SRGPU_E_ARG;
   std::lock_guard<std::mutex> lk(c->mu);
   if (threads) {
-    if (threads != 32 && threads != 64 && threads != 128 && threads != 256 && threads != 512) {
-      g_err = "threads must be 32, 64, 128, 256 or 512";
+    if (threads != 64 && threads != 128 && threads != 256 && threads != 512) {
+      g_err = "threads must be 64, 128, 256 or 512";
       return SRGPU_E_ARG;
     }
     c->threads = threads;
@@ -246,21 +250,60 @@ extern "C" int srgpu_set_sequences(srgpu_ctx* c, const srgpu_seqview* seqs, uint
     }
     rcsafe[i] = safe;
   }
+  // alphabet of the forward bytes plus what allwave's reverse complement can produce; the packing
+  // width is the smallest that recodes it injectively (2 bits for pure ACGT, 4 bits with N / soft
+  // masking, 8 bits = raw bytes otherwise)
+  bool seen[256] = {false};
+  for (uint32_t i = 0; i < n; ++i) {
+    const uint8_t* d = seqs[i].data;
+    for (uint64_t j = 0; j < seqs[i].len; ++j) seen[d[j]] = true;
+  }
+  bool any_other = false;
+  for (int b = 0; b < 256; ++b)
+    if (seen[b] && !strchr("ACGTacgt", b)) any_other = true;
+  if (seen['A'] || seen['a']) seen['T'] = true;
+  if (seen['T'] || seen['t']) seen['A'] = true;
+  if (seen['C'] || seen['c']) seen['G'] = true;
+  if (seen['G'] || seen['g']) seen['C'] = true;
+  if (any_other) seen['N'] = true;
+  CodeTable tab;
+  int nsym = 0;
+  for (int b = 0; b < 256; ++b) tab.code[b] = 0;
+  for (int b = 0; b < 256; ++b)
+    if (seen[b]) tab.code[b] = (uint8_t)(nsym++);
+  const int lbits = nsym <= 4 ? 1 : nsym <= 16 ? 2 : 3;
+  if (lbits == 3)
+    for (int b = 0; b < 256; ++b) tab.code[b] = (uint8_t)b;
+  std::vector<uint64_t> pk_off(n);
+  uint64_t pk_words = 4;
+  uint32_t max_pk = 0;
+  for (uint32_t i = 0; i < n; ++i) {
+    const uint64_t nw = ((((uint64_t)len[i] << lbits) + 31) >> 5);
+    const uint64_t nw4 = (nw + 3) & ~(uint64_t)3;
+    pk_off[i] = pk_words;
+    pk_words += nw4 + 8;  // 4 guard words after this sequence + 4 before the next
+    max_pk = std::max<uint32_t>(max_pk, (uint32_t)(nw4 + 8));
+  }
   int rc;
-  if ((rc = c->d_fwd.ensure(bytes)) || (rc = c->d_rc.ensure(bytes)) || (rc = c->d_byte_off.ensure(n)) ||
-      (rc = c->d_pos_off.ensure(n)) || (rc = c->d_len.ensure(n)) || (rc = c->d_rcsafe.ensure(n))) {
+  if ((rc = c->d_fwd.ensure(bytes)) || (rc = c->d_byte_off.ensure(n)) || (rc = c->d_pos_off.ensure(n)) ||
+      (rc = c->d_len.ensure(n)) || (rc = c->d_rcsafe.ensure(n)) || (rc = c->d_pk_off.ensure(n)) ||
+      (rc = c->d_pk_fwd.ensure(pk_words)) || (rc = c->d_pk_rc.ensure(pk_words))) {
     cudaFreeHost(stage);
     return rc;
   }
   cudaError_t e = cudaMemcpyAsync(c->d_fwd.p, stage, bytes, cudaMemcpyHostToDevice, c->stream);
-  if (e == cudaSuccess) e = cudaMemsetAsync(c->d_rc.p, 0, bytes, c->stream);
+  if (e == cudaSuccess) e = cudaMemsetAsync(c->d_pk_fwd.p, 0, pk_words * 4, c->stream);
+  if (e == cudaSuccess) e = cudaMemsetAsync(c->d_pk_rc.p, 0, pk_words * 4, c->stream);
   if (e == cudaSuccess && n) e = cudaMemcpyAsync(c->d_byte_off.p, byte_off.data(), n * 8, cudaMemcpyHostToDevice, c->stream);
   if (e == cudaSuccess && n) e = cudaMemcpyAsync(c->d_pos_off.p, pos_off.data(), n * 8, cudaMemcpyHostToDevice, c->stream);
+  if (e == cudaSuccess && n) e = cudaMemcpyAsync(c->d_pk_off.p, pk_off.data(), n * 8, cudaMemcpyHostToDevice, c->stream);
   if (e == cudaSuccess && n) e = cudaMemcpyAsync(c->d_len.p, len.data(), n * 4, cudaMemcpyHostToDevice, c->stream);
   if (e == cudaSuccess && n) e = cudaMemcpyAsync(c->d_rcsafe.p, rcsafe.data(), n, cudaMemcpyHostToDevice, c->stream);
   if (e == cudaSuccess && n) {
-    dim3 grid(std::max(1u, std::min(64u, (maxlen + 255) / 256)), std::min(n, 65535u));
-    rc_kernel<<<grid, 256, 0, c->stream>>>(c->d_fwd.p, c->d_rc.p, c->d_byte_off.p, c->d_len.p, n);
+    const uint32_t per = 32u >> lbits;
+    dim3 grid(std::max(1u, std::min(64u, (maxlen / per + 255) / 256)), std::min(n, 65535u));
+    pack_kernel<<<grid, 256, 0, c->stream>>>(c->d_fwd.p, c->d_byte_off.p, c->d_len.p, c->d_pk_off.p, c->d_pk_fwd.p,
+                                             c->d_pk_rc.p, tab, lbits, n);
     e = cudaGetLastError();
   }
   if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
@@ -269,6 +312,8 @@ extern "C" int srgpu_set_sequences(srgpu_ctx* c, const srgpu_seqview* seqs, uint
     g_err = std::string("set_sequences: ") + cudaGetErrorString(e);
     return SRGPU_E_CUDA;
   }
+  c->lbits = lbits;
+  c->max_pk_words = max_pk;
   c->n_seqs = n;
   c->total_len = pos;
   c->max_len = maxlen;
@@ -280,7 +325,10 @@ extern "C" int srgpu_set_sequences(srgpu_ctx* c, const srgpu_seqview* seqs, uint
 static SeqTable seq_table(srgpu_ctx* c) {
   SeqTable t;
   t.fwd = c->d_fwd.p;
-  t.rc = c->d_rc.p;
+  t.pk_fwd = c->d_pk_fwd.p;
+  t.pk_rc = c->d_pk_rc.p;
+  t.pk_off = c->d_pk_off.p;
+  t.lbits = c->lbits;
   t.byte_off = c->d_byte_off.p;
   t.len = c->d_len.p;
   t.pos_off = c->d_pos_off.p;
@@ -310,19 +358,50 @@ static int check_penalties(const srgpu_penalties* p, Penalties* out) {
 }
 
 template <int T, int C>
-static cudaError_t launch_align_tc(const AlignArgs& a, int grid, cudaStream_t s) {
-  align_kernel<T, C><<<grid, T, 0, s>>>(a);
+static cudaError_t launch_align_tc(const AlignArgs& a, int grid, size_t smem, cudaStream_t s) {
+  static size_t configured = 0;
+  if (smem > configured) {
+    cudaError_t e = cudaFuncSetAttribute(align_kernel<T, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    configured = smem;
+  }
+  align_kernel<T, C><<<grid, T, smem, s>>>(a);
   return cudaGetLastError();
 }
-static cudaError_t launch_align(const AlignArgs& a, int threads, int ctas, int grid, cudaStream_t s) {
-  if (threads == 32) return ctas >= 16 ? launch_align_tc<32, 16>(a, grid, s) : launch_align_tc<32, 8>(a, grid, s);
-  if (threads == 64) return ctas >= 16 ? launch_align_tc<64, 16>(a, grid, s) : launch_align_tc<64, 8>(a, grid, s);
-  if (threads == 128) return ctas >= 8 ? launch_align_tc<128, 8>(a, grid, s) : launch_align_tc<128, 4>(a, grid, s);
-  if (threads == 512) return ctas >= 2 ? launch_align_tc<512, 2>(a, grid, s) : launch_align_tc<512, 1>(a, grid, s);
-  if (ctas >= 4) return launch_align_tc<256, 4>(a, grid, s);
-  if (ctas >= 2) return launch_align_tc<256, 2>(a, grid, s);
-  return launch_align_tc<256, 1>(a, grid, s);
+// (threads, ctas_per_sm) -> instantiation; the second template argument only caps registers
+#define ALIGN_DISPATCH(FN, ...)                                                  \
+  do {                                                                           \
+    if (threads == 64) {                                                         \
+      if (ctas > 12) return FN<64, 16>(__VA_ARGS__);                             \
+      if (ctas > 8) return FN<64, 12>(__VA_ARGS__);                              \
+      return FN<64, 8>(__VA_ARGS__);                                             \
+    }                                                                            \
+    if (threads == 128) {                                                        \
+      if (ctas > 6) return FN<128, 8>(__VA_ARGS__);                              \
+      if (ctas > 5) return FN<128, 6>(__VA_ARGS__);                              \
+      if (ctas > 4) return FN<128, 5>(__VA_ARGS__);                              \
+      return FN<128, 4>(__VA_ARGS__);                                            \
+    }                                                                            \
+    if (threads == 512) {                                                        \
+      if (ctas > 1) return FN<512, 2>(__VA_ARGS__);                              \
+      return FN<512, 1>(__VA_ARGS__);                                            \
+    }                                                                            \
+    if (ctas > 3) return FN<256, 4>(__VA_ARGS__);                                \
+    if (ctas > 2) return FN<256, 3>(__VA_ARGS__);                                \
+    return FN<256, 2>(__VA_ARGS__);                                              \
+  } while (0)
+static cudaError_t launch_align(const AlignArgs& a, int threads, int ctas, int grid, size_t smem, cudaStream_t s) {
+  ALIGN_DISPATCH(launch_align_tc, a, grid, smem, s);
 }
+
+template <int T, int C>
+static int occ_tc(size_t smem) {
+  int nb = 0;
+  cudaFuncSetAttribute(align_kernel<T, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, align_kernel<T, C>, T, smem) != cudaSuccess) return 1;
+  return nb < 1 ? 1 : nb;
+}
+static int align_occupancy(int threads, int ctas, size_t smem) { ALIGN_DISPATCH(occ_tc, smem); }
 
 // core driver: pairs already on the device (d_pairs). Fills c->d_out (n_pairs records) and, per
 // chunk, runs the union kernel when uf != nullptr. When keep_runs, a single chunk is used and the
@@ -337,7 +416,15 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
     return SRGPU_E_ARG;
   }
   const uint32_t maxlen = c->max_len;
-  int grid = c->n_sm * c->ctas_per_sm;
+  // staged sequences: three packed sequences per CTA in dynamic shared memory when they fit
+  size_t smem = (size_t)3 * c->max_pk_words * 4;
+  uint32_t smem_seq_words = c->max_pk_words;
+  if (smem > (size_t)c->smem_budget) {
+    smem = 0;
+    smem_seq_words = 0;
+  }
+  const int resident = std::min(c->ctas_per_sm, align_occupancy(c->threads, c->ctas_per_sm, smem));
+  int grid = c->n_sm * resident;
   if ((uint64_t)grid > n_pairs) grid = (int)n_pairs;
   // workspace geometry
   const int fullW = (int)(2 * ((uint64_t)maxlen + 4));
@@ -377,6 +464,7 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
   a.runs_tmp = c->d_runs_tmp.p;
   a.bt_tmp = c->d_bt_tmp.p;
   a.runs_cap = (uint32_t)runs_cap;
+  a.smem_seq_words = smem_seq_words;
   a.arena = c->d_arena.p;
   a.arena_cap = arena_cap;
   a.arena_head = c->d_scalars.p;
@@ -422,9 +510,10 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
       a.ring = c->d_ring.p;
       a.ring_stride = (size_t)2 * pen.scope * 5 * curW;
       a.W = curW;
+      a.fixed_w = attempt > 0 ? 1 : 0;
       CK(cudaMemsetAsync(a.next_pair, 0, sizeof(unsigned int), c->stream));
       CK(cudaEventRecord(c->ev[1], c->stream));
-      cudaError_t e = launch_align(a, c->threads, c->ctas_per_sm, cur_grid, c->stream);
+      cudaError_t e = launch_align(a, c->threads, c->ctas_per_sm, cur_grid, smem, c->stream);
       if (e != cudaSuccess) {
         g_err = std::string("align_kernel launch: ") + cudaGetErrorString(e);
         return SRGPU_E_CUDA;

@@ -49,12 +49,18 @@ __device__ __forceinline__ bool uf_unite(uint32_t* __restrict__ parent, uint32_t
 
 // ---------------------------------------------------------------------------
 struct SeqTable {
-  const uint8_t* fwd;        // padded concatenation, forward bytes
-  const uint8_t* rc;         // same layout, allwave reverse complement (allwave/src/alignment.rs:174-186)
-  const uint64_t* byte_off;  // start of sequence i inside fwd/rc
+  const uint8_t* fwd;        // padded concatenation, forward bytes (union kernel / process_alignment)
+  const uint64_t* byte_off;  // start of sequence i inside fwd
   const uint32_t* len;
   const uint64_t* pos_off;   // offset in the concatenated Pos space (src/seqrush.rs:1816-1818)
   const uint8_t* rc_safe;    // 1 when every byte is in ACGTacgtN: allwave RC == seqrush per-base RC
+  // packed copies for the aligner: 1 << lbits bits per symbol, forward and allwave reverse
+  // complement (allwave/src/alignment.rs:174-186); word 0 of sequence i at pk_off[i] (16-byte
+  // aligned, 4 guard words on both sides)
+  const uint32_t* pk_fwd;
+  const uint32_t* pk_rc;
+  const uint64_t* pk_off;
+  int lbits;
   uint32_t n;
 };
 
@@ -75,7 +81,8 @@ struct AlignArgs {
   // per-CTA workspace (indexed by blockIdx.x)
   int32_t* ring;
   size_t ring_stride;  // ints per CTA = 2*scope*5*W
-  int W;
+  int W;               // widest ring row this launch can address
+  int fixed_w;         // 1: every pair uses W (retry launches); 0: rows are sized per pair from its edit distance
   int32_t* full;
   size_t full_stride;  // ints per CTA = 5*cap*cap
   WfMeta* full_meta;   // cap*5 per CTA
@@ -86,6 +93,7 @@ struct AlignArgs {
   uint32_t* runs_tmp;
   uint32_t* bt_tmp;
   uint32_t runs_cap;  // per CTA
+  uint32_t smem_seq_words;  // words per staged sequence (0: sequences are read from global memory)
   // outputs
   PairOut* out;
   uint32_t* arena;
@@ -97,11 +105,42 @@ struct AlignArgs {
 
 static constexpr int ST_ARENA_OVERFLOW = 6;
 
+// ---- bulk asynchronous copy global -> shared (TMA engine, 1-D form) completing on an mbarrier ----
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t done = 0;
+  while (!done) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(done)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+  }
+}
+
 template <int THREADS, int MIN_CTAS>
 __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
+  extern __shared__ __align__(16) uint32_t s_seq[];  // [Pf | Pr | T], smem_seq_words each
   __shared__ CtaShared sh;
   __shared__ unsigned int s_pair;
   __shared__ unsigned int s_cnt[8];
+  __shared__ __align__(8) uint64_t s_bar;
   Ctx cx;
   cx.sh = &sh;
   cx.tid = threadIdx.x;
@@ -110,8 +149,6 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
   const size_t b = blockIdx.x;
   PairWorkspace ws;
   ws.ring_f = a.ring + b * a.ring_stride;
-  ws.ring_r = ws.ring_f + a.ring_stride / 2;
-  ws.W = a.W;
   ws.full = a.full + b * a.full_stride;
   ws.full_meta = a.full_meta + b * (size_t)a.cap * 5;
   ws.cap = a.cap;
@@ -121,6 +158,10 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
   ro.bt = a.bt_tmp + b * (size_t)a.runs_cap;
   ro.bt_cap = a.runs_cap;
   int32_t* obuf = a.orient + b * a.orient_stride;
+  const int lbits = a.seqs.lbits;
+  const bool staged = a.smem_seq_words != 0;
+  uint32_t phase = 0;
+  if (staged && threadIdx.x == 0) mbar_init(&s_bar, 1);
   while (true) {
     __syncthreads();
     if (threadIdx.x == 0) s_pair = atomicAdd(a.next_pair, 1u);
@@ -130,15 +171,42 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
     const unsigned int pi = a.todo ? a.todo[slot] : slot;
     const uint2 pr = a.pairs[pi];
     const uint32_t plen = a.seqs.len[pr.x], tlen = a.seqs.len[pr.y];
-    const uint8_t* Pf = a.seqs.fwd + a.seqs.byte_off[pr.x];
-    const uint8_t* Pr = a.seqs.rc + a.seqs.byte_off[pr.x];
-    const uint8_t* T = a.seqs.fwd + a.seqs.byte_off[pr.y];
+    const uint32_t* Pf = a.seqs.pk_fwd + a.seqs.pk_off[pr.x];
+    const uint32_t* Pr = a.seqs.pk_rc + a.seqs.pk_off[pr.x];
+    const uint32_t* T = a.seqs.pk_fwd + a.seqs.pk_off[pr.y];
+    if (staged) {
+      // stage the three packed sequences (with their guard words) into shared memory
+      const uint32_t wp = 8 + (((((plen << lbits) + 31) >> 5) + 3) & ~3u);
+      const uint32_t wt = 8 + (((((tlen << lbits) + 31) >> 5) + 3) & ~3u);
+      if (threadIdx.x == 0) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        mbar_expect_tx(&s_bar, (2 * wp + wt) * 4);
+        bulk_g2s(s_seq, Pf - 4, wp * 4, &s_bar);
+        bulk_g2s(s_seq + a.smem_seq_words, Pr - 4, wp * 4, &s_bar);
+        bulk_g2s(s_seq + 2 * a.smem_seq_words, T - 4, wt * 4, &s_bar);
+      }
+      mbar_wait(&s_bar, phase);
+      phase ^= 1;
+      Pf = s_seq + 4;
+      Pr = s_seq + a.smem_seq_words + 4;
+      T = s_seq + 2 * a.smem_seq_words + 4;
+    }
     // 1. strand (allwave/src/alignment.rs:24-30)
-    const OrientResult orr = wf_orient(cx, Pf, Pr, T, (int)plen, (int)tlen, obuf, a.orient_row);
-    // 2. BiWFA (allwave/src/alignment.rs:189-276)
+    const OrientResult orr = wf_orient(cx, Pf, Pr, T, lbits, (int)plen, (int)tlen, obuf, a.orient_row);
+    // 2. BiWFA (allwave/src/alignment.rs:189-276). Ring rows are sized from the edit distance just
+    //    found (penalty <= 10 per edit, about half of it per direction); a pair that still
+    //    overflows is reported and re-run by the host with full-width rows.
+    int W = a.W;
+    if (!a.fixed_w) {
+      const long long est = ((8ll * orr.distance + 512) + 63) & ~63ll;
+      if (est < W) W = (int)est;
+    }
+    ws.W = W;
+    ws.ring_r = ws.ring_f + (size_t)a.pen.scope * 5 * W;
     SeqView sv;
     sv.p = orr.is_reverse ? Pr : Pf;
     sv.t = T;
+    sv.lbits = lbits;
     const PairResult r = wf_align_pair(cx, sv, (int)plen, (int)tlen, a.pen, ws, ro);
     // 3. finalize: CIGAR statistics (allwave/src/alignment.rs:279-324), penalty
     //    (WFA2-lib/alignment/cigar.c:303-343), copy the runs into the chunk arena
@@ -212,25 +280,46 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
 }
 
 // ---------------------------------------------------------------------------
-// allwave reverse complement of every sequence (allwave/src/alignment.rs:174-186)
+// Pack every sequence, forward and allwave reverse complement (allwave/src/alignment.rs:174-186:
+// ACGT/acgt -> upper-case complement, anything else -> 'N'), at 1 << lbits bits per symbol through
+// an injective byte -> code table (identity for 8 bits). One thread per output word.
 // ---------------------------------------------------------------------------
-__global__ void rc_kernel(const uint8_t* __restrict__ fwd, uint8_t* __restrict__ rc, const uint64_t* __restrict__ byte_off,
-                          const uint32_t* __restrict__ len, uint32_t n) {
+struct CodeTable {
+  uint8_t code[256];
+};
+__device__ __forceinline__ uint8_t allwave_comp(uint8_t c) {
+  switch (c) {
+    case 'A': case 'a': return 'T';
+    case 'T': case 't': return 'A';
+    case 'C': case 'c': return 'G';
+    case 'G': case 'g': return 'C';
+    default: return 'N';
+  }
+}
+__global__ void pack_kernel(const uint8_t* __restrict__ fwd, const uint64_t* __restrict__ byte_off,
+                            const uint32_t* __restrict__ len, const uint64_t* __restrict__ pk_off,
+                            uint32_t* __restrict__ pk_fwd, uint32_t* __restrict__ pk_rc, CodeTable tab, int lbits, uint32_t n) {
+  __shared__ uint8_t s_code[256];
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) s_code[i] = tab.code[i];
+  __syncthreads();
+  const uint32_t per = 32u >> lbits, bits = 1u << lbits;
   for (uint32_t s = blockIdx.y; s < n; s += gridDim.y) {
     const uint32_t L = len[s];
+    const uint32_t nw = (L + per - 1) / per;
     const uint8_t* src = fwd + byte_off[s];
-    uint8_t* dst = rc + byte_off[s];
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < L; i += gridDim.x * blockDim.x) {
-      const uint8_t c = src[L - 1 - i];
-      uint8_t o = 'N';
-      switch (c) {
-        case 'A': case 'a': o = 'T'; break;
-        case 'T': case 't': o = 'A'; break;
-        case 'C': case 'c': o = 'G'; break;
-        case 'G': case 'g': o = 'C'; break;
-        default: o = 'N'; break;
+    uint32_t* df = pk_fwd + pk_off[s];
+    uint32_t* dr = pk_rc + pk_off[s];
+    for (uint32_t w = blockIdx.x * blockDim.x + threadIdx.x; w < nw; w += gridDim.x * blockDim.x) {
+      uint32_t vf = 0, vr = 0;
+      for (uint32_t j = 0; j < per; ++j) {
+        const uint32_t i = w * per + j;
+        if (i < L) {
+          vf |= (uint32_t)s_code[src[i]] << (j * bits);
+          vr |= (uint32_t)s_code[allwave_comp(src[L - 1 - i])] << (j * bits);
+        }
       }
-      dst[i] = o;
+      df[w] = vf;
+      dr[w] = vr;
     }
   }
 }

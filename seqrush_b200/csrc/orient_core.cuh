@@ -18,8 +18,8 @@ struct OrientResult {
 };
 
 // buf: 4 rows (strand x parity) of `stride` ints each; stride >= plen + tlen + 3.
-WFA_FN OrientResult wf_orient(Ctx& cx, const uint8_t* Pf, const uint8_t* Pr, const uint8_t* T, int plen, int tlen,
-                              int32_t* buf, int stride) {
+WFA_FN OrientResult wf_orient(Ctx& cx, const uint32_t* Pf, const uint32_t* Pr, const uint32_t* T, int lbits, int plen,
+                              int tlen, int32_t* buf, int stride) {
   OrientResult res;
   res.is_reverse = 0;
   res.distance = 0;
@@ -29,9 +29,9 @@ WFA_FN OrientResult wf_orient(Ctx& cx, const uint8_t* Pf, const uint8_t* Pr, con
   if (cx.tid == 0) {
     cx.sh->ocells = 0;
     for (int strand = 0; strand < 2; ++strand) {
-      const uint8_t* P = strand ? Pr : Pf;
+      const uint32_t* P = strand ? Pr : Pf;
       int32_t* row = buf + (size_t)(strand * 2 + 0) * stride + center;
-      row[0] = lcp_fwd(P, T, imin(plen, tlen));
+      row[0] = lcp_fwd(P, T, 0, 0, imin(plen, tlen), lbits);
     }
   }
   cta_sync();
@@ -62,7 +62,7 @@ WFA_FN OrientResult wf_orient(Ctx& cx, const uint8_t* Pf, const uint8_t* Pr, con
     for (int idx = cx.tid; idx < 2 * width; idx += cx.nt) {
       const int strand = idx >= width;
       const int k = lo + (strand ? idx - width : idx);
-      const uint8_t* P = strand ? Pr : Pf;
+      const uint32_t* P = strand ? Pr : Pf;
       const int32_t* prev = buf + (size_t)(strand * 2 + par) * stride + center;
       int32_t* cur = buf + (size_t)(strand * 2 + (par ^ 1)) * stride + center;
       int32_t best = OFFSET_NULL;
@@ -80,7 +80,7 @@ WFA_FN OrientResult wf_orient(Ctx& cx, const uint8_t* Pf, const uint8_t* Pr, con
       }
       if (best != OFFSET_NULL) {
         const int v = best - k;
-        best += lcp_fwd(P + v, T + best, imin(plen - v, tlen - best));
+        best += lcp_fwd(P, T, v, best, imin(plen - v, tlen - best), lbits);
       }
       cur[k] = best;
     }

@@ -77,12 +77,15 @@ struct Frame {
   int level;
 };
 
-// Sequence view: raw bytes (any alphabet; byte equality like the reference,
-// WFA/wavefront_extend_kernels.c:68-92). Buffers are padded by >= 8 bytes on
-// both sides so that word loads never leave the allocation.
+// Sequence view: packed symbols, 1 << lbits bits each (lbits 1/2/3 = 2/4/8 bits per base), base i
+// at bit (i << lbits) of a little-endian uint32 word array. The packing is an injective recoding
+// of the bytes, so symbol equality == byte equality (the reference compares raw bytes,
+// WFA/wavefront_extend_kernels.c:68-92). Arrays carry >= 1 guard word on both sides; they live
+// in shared memory (staged per pair by a bulk copy) or, for oversized pairs, in global memory.
 struct SeqView {
-  const uint8_t* p;  // pattern (query, possibly reverse-complemented)
-  const uint8_t* t;  // text (target)
+  const uint32_t* p;  // pattern (query, possibly reverse-complemented)
+  const uint32_t* t;  // text (target)
+  int lbits;
 };
 
 // ---------------------------------------------------------------------------
@@ -96,13 +99,30 @@ struct SeqView {
 struct WfStore {
   int32_t* base;
   WfMeta* meta;  // [slots*5]
+  int* ub;       // [slots*5] upper bound of the max antidiagonal (2h-k) over the row (modular only)
   int modular;
   int scope;
   int W;    // modular: diagonals per row
   int cap;  // full: max score + 1
-  WFA_FN int slot(int s) const { return modular ? (s % scope) : s; }
+  int cur_s, cur_slot;  // modular: slot of score cur_s (avoids an integer modulo per access)
+  WFA_FN void set_cur(int s) {
+    if (!modular) return;
+    if (s == cur_s + 1) {
+      cur_slot = (cur_slot + 1 == scope) ? 0 : cur_slot + 1;
+    } else if (s != cur_s) {
+      cur_slot = s % scope;
+    }
+    cur_s = s;
+  }
+  // valid for cur_s - scope < s <= cur_s
+  WFA_FN int slot(int s) const {
+    if (!modular) return s;
+    const int t = cur_slot - (cur_s - s);
+    return t < 0 ? t + scope : t;
+  }
+  WFA_FN int32_t* row_of_slot(int sl, int c) const { return base + ((size_t)(sl * 5 + c)) * (size_t)W + (W >> 1); }
   WFA_FN int32_t* row(int s, int c) const {
-    if (modular) return base + ((size_t)((s % scope) * 5 + c)) * (size_t)W + (W >> 1);
+    if (modular) return row_of_slot(slot(s), c);
     return base + (size_t)c * (size_t)cap * (size_t)cap + (size_t)s * (size_t)s + s;
   }
   WFA_FN WfMeta get(int s, int c) const {
@@ -135,6 +155,8 @@ struct RedSlots {
 struct CtaShared {
   WfMeta meta_f[MAX_SCOPE * 5];
   WfMeta meta_r[MAX_SCOPE * 5];
+  int ub_f[MAX_SCOPE * 5];
+  int ub_r[MAX_SCOPE * 5];
   RedSlots red[2];
   int ovl[MAX_SCOPE * 5];  // overlap search results (min k_0 per task)
   Frame stack[STACK_MAX];
@@ -188,54 +210,65 @@ WFA_FN int imax(int a, int b) { return a > b ? a : b; }
 // complemented) copies (WFA/wavefront_sequences.c:83-101): P[-1-v-i] vs T[-1-h-i]
 // relative to the end pointers, i.e. a common *suffix* walk on the originals.
 // ---------------------------------------------------------------------------
-WFA_FN uint32_t load_u32_unaligned(const uint8_t* a) {
+WFA_FN uint32_t funnel_r(uint32_t lo, uint32_t hi, uint32_t sh) {
 #if WFA_DEVICE
-  const uintptr_t ad = (uintptr_t)a;
-  const uint32_t* w = (const uint32_t*)(ad & ~(uintptr_t)3);
-  const uint32_t lo = w[0], hi = w[1];
-  return __funnelshift_r(lo, hi, (uint32_t)(ad & 3) * 8);
+  return __funnelshift_r(lo, hi, sh);
 #else
-  uint32_t v;
-  memcpy(&v, a, 4);
-  return v;
+  sh &= 31;
+  return sh ? ((lo >> sh) | (hi << (32 - sh))) : lo;
 #endif
 }
-
-WFA_FN int lcp_fwd(const uint8_t* p, const uint8_t* t, int maxlen) {
-  // p,t point at the first bytes to compare
-  int n = 0;
-  if (maxlen <= 0) return 0;
-  if (p[0] != t[0]) return 0;
-  while (n < maxlen) {
-    const uint32_t x = load_u32_unaligned(p + n) ^ load_u32_unaligned(t + n);
-    if (x) {
+WFA_FN int ctz32(uint32_t x) {
 #if WFA_DEVICE
-      n += (__ffs((int)x) - 1) >> 3;
+  return __ffs((int)x) - 1;
 #else
-      n += __builtin_ctz(x) >> 3;
+  return __builtin_ctz(x);
 #endif
+}
+WFA_FN int clz32(uint32_t x) {
+#if WFA_DEVICE
+  return __clz((int)x);
+#else
+  return __builtin_clz(x);
+#endif
+}
+// 32 bits of packed symbols starting at symbol index i (forward window)
+WFA_FN uint32_t pk_window_fwd(const uint32_t* a, int i, int lbits) {
+  const uint32_t bit = (uint32_t)i << lbits;
+  const uint32_t* w = a + (bit >> 5);
+  return funnel_r(w[0], w[1], bit);
+}
+// 32 bits of packed symbols ending with symbol index i in the top bits (backward window)
+WFA_FN uint32_t pk_window_rev(const uint32_t* a, int i, int lbits) {
+  const uint32_t bit = (uint32_t)(i + 1) << lbits;  // exclusive end
+  const uint32_t* w = a + (bit >> 5);
+  return funnel_r(w[-1], w[0], bit);
+}
+// common prefix of P[v..] and T[h..], at most maxlen symbols (XOR + count-trailing-zeros on packed words)
+WFA_FN int lcp_fwd(const uint32_t* P, const uint32_t* T, int v, int h, int maxlen, int lbits) {
+  int n = 0;
+  const int per = 32 >> lbits;
+  while (n < maxlen) {
+    const uint32_t x = pk_window_fwd(P, v + n, lbits) ^ pk_window_fwd(T, h + n, lbits);
+    if (x) {
+      n += ctz32(x) >> lbits;
       break;
     }
-    n += 4;
+    n += per;
   }
   return n < maxlen ? n : maxlen;
 }
-WFA_FN int lcp_rev(const uint8_t* p, const uint8_t* t, int maxlen) {
-  // p,t point at the first (highest-address) bytes to compare; walk downwards
+// common suffix walk: P[v], P[v-1], ... against T[h], T[h-1], ...
+WFA_FN int lcp_rev(const uint32_t* P, const uint32_t* T, int v, int h, int maxlen, int lbits) {
   int n = 0;
-  if (maxlen <= 0) return 0;
-  if (p[0] != t[0]) return 0;
+  const int per = 32 >> lbits;
   while (n < maxlen) {
-    const uint32_t x = load_u32_unaligned(p - n - 3) ^ load_u32_unaligned(t - n - 3);
+    const uint32_t x = pk_window_rev(P, v - n, lbits) ^ pk_window_rev(T, h - n, lbits);
     if (x) {
-#if WFA_DEVICE
-      n += __clz((int)x) >> 3;
-#else
-      n += __builtin_clz(x) >> 3;
-#endif
+      n += clz32(x) >> lbits;
       break;
     }
-    n += 4;
+    n += per;
   }
   return n < maxlen ? n : maxlen;
 }
@@ -243,8 +276,10 @@ WFA_FN int lcp_rev(const uint8_t* p, const uint8_t* t, int maxlen) {
 // One aligner direction over the current sub-problem.
 struct Dir {
   WfStore st;
-  const uint8_t* P;  // forward: &pattern[pb]; reverse: &pattern[pe-1]
-  const uint8_t* T;
+  const uint32_t* P;  // packed pattern / text (whole sequences)
+  const uint32_t* T;
+  int p0, t0;  // forward: first symbol of the sub-problem (pb, tb); reverse: last symbol (pe-1, te-1)
+  int lbits;
   int plen, tlen;
   int reverse;
   int cbegin, cend;
@@ -256,7 +291,10 @@ WFA_FN int32_t rd(const int32_t* row, WfMeta m, int k) { return (k >= m.lo && k 
 // Initial wavefront (WFA/wavefront_aligner.c:252-383, end-to-end form only).
 // Executed by thread 0; caller syncs.
 // ---------------------------------------------------------------------------
-WFA_FN void wf_init(const Dir& d) {
+static constexpr int UB_NONE = INT32_MIN / 4;  // "row cannot overlap anything"
+
+WFA_FN void wf_init(Dir& d) {
+  d.st.set_cur(0);
   for (int c = 0; c < 5; ++c) {
     WfMeta m;
     m.lo = 1;
@@ -267,6 +305,7 @@ WFA_FN void wf_init(const Dir& d) {
       d.st.row(0, c)[0] = 0;
     }
     d.st.meta[d.st.slot(0) * 5 + c] = m;
+    if (d.st.ub) d.st.ub[d.st.slot(0) * 5 + c] = (c == d.cbegin) ? 0 : UB_NONE;
   }
 }
 
@@ -291,17 +330,19 @@ WFA_FN bool wf_end_reached(const Dir& d, int score) {
 WFA_FN int wf_extend_cell(const Dir& d, int k, int32_t off) {
   const int v = off - k, h = off;
   const int room = imin(d.plen - v, d.tlen - h);
-  if (!d.reverse) return off + lcp_fwd(d.P + v, d.T + h, room);
-  return off + lcp_rev(d.P - v, d.T - h, room);
+  if (!d.reverse) return off + lcp_fwd(d.P, d.T, d.p0 + v, d.t0 + h, room, d.lbits);
+  return off + lcp_rev(d.P, d.T, d.p0 - v, d.t0 - h, room, d.lbits);
 }
 
-// score-0 extension: a single cell at most (k=0), done by thread 0.
-WFA_FN StepOut wf_extend0(Ctx& cx, const Dir& d) {
+// score-0 extension: a single cell at most (k=0), done by thread 0. Every thread runs set_cur so
+// that the per-thread slot arithmetic stays in step.
+WFA_FN StepOut wf_extend0(Ctx& cx, Dir& d) {
   StepOut o;
   o.null_step = 0;
   o.end_reached = 0;
   o.max_ak = 0;
   o.overflow = 0;
+  d.st.set_cur(0);
   cta_sync();
   if (cx.tid == 0) {
     const WfMeta m = d.st.get(0, C_M);
@@ -311,6 +352,7 @@ WFA_FN StepOut wf_extend0(Ctx& cx, const Dir& d) {
       const int32_t e = wf_extend_cell(d, 0, row[0]);
       row[0] = e;
       ak = 2 * e;
+      if (d.st.ub) d.st.ub[d.st.slot(0) * 5 + C_M] = ak;
     }
     cx.sh->bcast[0] = ak;
   }
@@ -320,20 +362,51 @@ WFA_FN StepOut wf_extend0(Ctx& cx, const Dir& d) {
   return o;
 }
 
+#if WFA_DEVICE
+static constexpr int LANES = 32;
+WFA_FN uint32_t warp_ballot(bool p) { return __ballot_sync(0xffffffffu, p); }
+#else
+static constexpr int LANES = 1;
+WFA_FN uint32_t warp_ballot(bool p) { return p ? 1u : 0u; }
+#endif
+
+// warp-uniform first/last valid diagonal of one component, fed with one ballot per 32-diagonal chunk
+struct Span {
+  int mn, mx;
+  WFA_FN void init() {
+    mn = INT32_MAX;
+    mx = INT32_MIN;
+  }
+  WFA_FN void add(uint32_t b, int kb) {
+    if (b) {
+      if (mn == INT32_MAX) mn = kb + ctz32(b);
+      mx = kb + 31 - clz32(b);
+    }
+  }
+};
+
+WFA_FN bool in_bounds(int32_t h, int k, uint32_t tlen, uint32_t plen) {
+  return (uint32_t)h <= tlen && (uint32_t)(h - k) <= plen;
+}
+
 // ---------------------------------------------------------------------------
 // One score step: next wavefront (WFA/wavefront_compute_affine2p.c:45-106,
 // 334-368; limits WFA/wavefront_compute.c:40-86; trimming :579-632) fused with
 // the exact-match extension of the new M wavefront (WFA/wavefront_extend.c:
-// 86-121,173-211) and the end test. Diagonals are distributed over the CTA's
-// threads; per-component trims and the max antidiagonal are warp-reduced and
-// merged with shared-memory atomics.
+// 86-121,173-211) and the end test.
+// Layout: each warp takes 32-diagonal chunks. Chunks that lie inside the
+// interior of all seven source wavefronts read them without range checks;
+// fringe chunks use checked reads. The per-component trims (first/last
+// in-bounds diagonal) come from one ballot per chunk and component instead of
+// per-cell min/max; the max antidiagonal is a per-lane running max.
 // ---------------------------------------------------------------------------
-WFA_FN StepOut wf_step(Ctx& cx, const Dir& d, const Penalties& pen, int s) {
+WFA_FN StepOut wf_step(Ctx& cx, Dir& d, const Penalties& pen, int s) {
   StepOut o;
   o.null_step = 0;
   o.end_reached = 0;
   o.max_ak = 0;
   o.overflow = 0;
+  d.st.set_cur(s);
   cta_sync();  // metas written by thread 0 in the previous step are visible; red[parity] is reset
   const WfStore& st = d.st;
   const int s_mis = s - pen.x, s_o1 = s - pen.o1 - pen.e1, s_e1 = s - pen.e1;
@@ -350,6 +423,7 @@ WFA_FN StepOut wf_step(Ctx& cx, const Dir& d, const Penalties& pen, int s) {
       for (int c = 0; c < 5; ++c) {
         st.meta[slot5 + c].lo = 1;
         st.meta[slot5 + c].hi = -1;
+        if (st.ub) st.ub[slot5 + c] = UB_NONE;
       }
     }
     o.null_step = 1;
@@ -381,6 +455,12 @@ WFA_FN StepOut wf_step(Ctx& cx, const Dir& d, const Penalties& pen, int s) {
   if (cx.tid == 0) cx.sh->cells += (unsigned long long)(hi - lo + 1);
   // output allocation (WFA/wavefront_compute.c:458-505)
   const bool a_i1 = !n_o1 || !n_i1, a_d1 = !n_o1 || !n_d1, a_i2 = !n_o2 || !n_i2, a_d2 = !n_o2 || !n_d2;
+  // interior: diagonals where all twelve reads fall inside their source wavefronts
+  int in_lo = 1, in_hi = 0;
+  if (!(n_mis || n_o1 || n_o2 || n_i1 || n_d1 || n_i2 || n_d2)) {
+    in_lo = imax(imax(m_mis.lo, imax(m_o1.lo, m_o2.lo) + 1), imax(imax(m_i1.lo, m_i2.lo) + 1, imax(m_d1.lo, m_d2.lo) - 1));
+    in_hi = imin(imin(m_mis.hi, imin(m_o1.hi, m_o2.hi) - 1), imin(imin(m_i1.hi, m_i2.hi) + 1, imin(m_d1.hi, m_d2.hi) - 1));
+  }
   const int32_t* r_mis = st.row(s_mis < 0 ? 0 : s_mis, C_M);
   const int32_t* r_o1 = st.row(s_o1 < 0 ? 0 : s_o1, C_M);
   const int32_t* r_o2 = st.row(s_o2 < 0 ? 0 : s_o2, C_M);
@@ -394,88 +474,98 @@ WFA_FN StepOut wf_step(Ctx& cx, const Dir& d, const Penalties& pen, int s) {
   int32_t* w_d1 = st.row(s, C_D1);
   int32_t* w_d2 = st.row(s, C_D2);
   const uint32_t tlen = (uint32_t)d.tlen, plen = (uint32_t)d.plen;
-  int mn0 = INT32_MAX, mn1 = INT32_MAX, mn2 = INT32_MAX, mn3 = INT32_MAX, mn4 = INT32_MAX;
-  int mx0 = INT32_MIN, mx1 = INT32_MIN, mx2 = INT32_MIN, mx3 = INT32_MIN, mx4 = INT32_MIN;
+  Span sp0, sp1, sp2, sp3, sp4;
+  sp0.init();
+  sp1.init();
+  sp2.init();
+  sp3.init();
+  sp4.init();
   int max_ak = 0;
-  for (int k = lo + cx.tid; k <= hi; k += cx.nt) {
-    const int32_t o1m = rd(r_o1, m_o1, k - 1), o1p = rd(r_o1, m_o1, k + 1);
-    const int32_t o2m = rd(r_o2, m_o2, k - 1), o2p = rd(r_o2, m_o2, k + 1);
-    const int32_t ins1 = imax(o1m, rd(r_i1, m_i1, k - 1)) + 1;
-    const int32_t ins2 = imax(o2m, rd(r_i2, m_i2, k - 1)) + 1;
-    const int32_t del1 = imax(o1p, rd(r_d1, m_d1, k + 1));
-    const int32_t del2 = imax(o2p, rd(r_d2, m_d2, k + 1));
-    const int32_t mis = rd(r_mis, m_mis, k) + 1;
-    int32_t mx = imax(imax(del1, del2), imax(mis, imax(ins1, ins2)));
-    if ((uint32_t)mx > tlen || (uint32_t)(mx - k) > plen) mx = OFFSET_NULL;
+  const int lane = lane_id();
+#if WFA_DEVICE
+  const int warp = cx.tid >> 5, nwarps = cx.nt >> 5;
+#else
+  const int warp = 0, nwarps = 1;
+#endif
+  for (int kb = lo + warp * LANES; kb <= hi; kb += nwarps * LANES) {
+    const int k = kb + lane;
+    const bool act = k <= hi;
+    int32_t o1m, o1p, o2m, o2p, i1, d1, i2, d2, mis;
+    if (kb >= in_lo && kb + LANES - 1 <= in_hi) {
+      o1m = r_o1[k - 1];
+      o1p = r_o1[k + 1];
+      o2m = r_o2[k - 1];
+      o2p = r_o2[k + 1];
+      i1 = r_i1[k - 1];
+      d1 = r_d1[k + 1];
+      i2 = r_i2[k - 1];
+      d2 = r_d2[k + 1];
+      mis = r_mis[k];
+    } else {
+      o1m = rd(r_o1, m_o1, k - 1);
+      o1p = rd(r_o1, m_o1, k + 1);
+      o2m = rd(r_o2, m_o2, k - 1);
+      o2p = rd(r_o2, m_o2, k + 1);
+      i1 = rd(r_i1, m_i1, k - 1);
+      d1 = rd(r_d1, m_d1, k + 1);
+      i2 = rd(r_i2, m_i2, k - 1);
+      d2 = rd(r_d2, m_d2, k + 1);
+      mis = rd(r_mis, m_mis, k);
+    }
+    const int32_t ins1 = imax(o1m, i1) + 1;
+    const int32_t ins2 = imax(o2m, i2) + 1;
+    const int32_t del1 = imax(o1p, d1);
+    const int32_t del2 = imax(o2p, d2);
+    int32_t mx = imax(imax(del1, del2), imax(mis + 1, imax(ins1, ins2)));
+    const bool vm = act && in_bounds(mx, k, tlen, plen);
+    if (!vm) mx = OFFSET_NULL;
+    sp0.add(warp_ballot(vm), kb);
     if (a_i1) {
-      w_i1[k] = ins1;
-      if ((uint32_t)ins1 <= tlen && (uint32_t)(ins1 - k) <= plen) {
-        mn1 = imin(mn1, k);
-        mx1 = k;
-      }
+      if (act) w_i1[k] = ins1;
+      sp1.add(warp_ballot(act && in_bounds(ins1, k, tlen, plen)), kb);
     }
     if (a_i2) {
-      w_i2[k] = ins2;
-      if ((uint32_t)ins2 <= tlen && (uint32_t)(ins2 - k) <= plen) {
-        mn2 = imin(mn2, k);
-        mx2 = k;
-      }
+      if (act) w_i2[k] = ins2;
+      sp2.add(warp_ballot(act && in_bounds(ins2, k, tlen, plen)), kb);
     }
     if (a_d1) {
-      w_d1[k] = del1;
-      if ((uint32_t)del1 <= tlen && (uint32_t)(del1 - k) <= plen) {
-        mn3 = imin(mn3, k);
-        mx3 = k;
-      }
+      if (act) w_d1[k] = del1;
+      sp3.add(warp_ballot(act && in_bounds(del1, k, tlen, plen)), kb);
     }
     if (a_d2) {
-      w_d2[k] = del2;
-      if ((uint32_t)del2 <= tlen && (uint32_t)(del2 - k) <= plen) {
-        mn4 = imin(mn4, k);
-        mx4 = k;
-      }
+      if (act) w_d2[k] = del2;
+      sp4.add(warp_ballot(act && in_bounds(del2, k, tlen, plen)), kb);
     }
-    if (mx != OFFSET_NULL) {
-      mn0 = imin(mn0, k);
-      mx0 = k;
+    if (vm) {
       mx = wf_extend_cell(d, k, mx);
       max_ak = imax(max_ak, 2 * mx - k);
     }
-    w_m[k] = mx;
+    if (act) w_m[k] = mx;
   }
-  // merge per-thread trims (WFA/wavefront_compute.c:579-611 does the same with two linear scans)
+  // merge the per-warp trims (WFA/wavefront_compute.c:579-611 does the same with two linear scans)
   RedSlots* red = &cx.sh->red[cx.parity];
-  {
-    int v;
-    v = warp_min(mn0);
-    if (lane_id() == 0 && v != INT32_MAX) sh_atomic_min(&red->mn[0], v);
-    v = warp_max(mx0);
-    if (lane_id() == 0 && v != INT32_MIN) sh_atomic_max(&red->mx[0], v);
-    v = warp_max(max_ak);
-    if (lane_id() == 0 && v > 0) sh_atomic_max(&red->max_ak, v);
-    if (a_i1) {
-      v = warp_min(mn1);
-      if (lane_id() == 0 && v != INT32_MAX) sh_atomic_min(&red->mn[1], v);
-      v = warp_max(mx1);
-      if (lane_id() == 0 && v != INT32_MIN) sh_atomic_max(&red->mx[1], v);
+  max_ak = warp_max(max_ak);
+  if (lane == 0) {
+    if (max_ak > 0) sh_atomic_max(&red->max_ak, max_ak);
+    if (sp0.mn != INT32_MAX) {
+      sh_atomic_min(&red->mn[0], sp0.mn);
+      sh_atomic_max(&red->mx[0], sp0.mx);
     }
-    if (a_i2) {
-      v = warp_min(mn2);
-      if (lane_id() == 0 && v != INT32_MAX) sh_atomic_min(&red->mn[2], v);
-      v = warp_max(mx2);
-      if (lane_id() == 0 && v != INT32_MIN) sh_atomic_max(&red->mx[2], v);
+    if (sp1.mn != INT32_MAX) {
+      sh_atomic_min(&red->mn[1], sp1.mn);
+      sh_atomic_max(&red->mx[1], sp1.mx);
     }
-    if (a_d1) {
-      v = warp_min(mn3);
-      if (lane_id() == 0 && v != INT32_MAX) sh_atomic_min(&red->mn[3], v);
-      v = warp_max(mx3);
-      if (lane_id() == 0 && v != INT32_MIN) sh_atomic_max(&red->mx[3], v);
+    if (sp2.mn != INT32_MAX) {
+      sh_atomic_min(&red->mn[2], sp2.mn);
+      sh_atomic_max(&red->mx[2], sp2.mx);
     }
-    if (a_d2) {
-      v = warp_min(mn4);
-      if (lane_id() == 0 && v != INT32_MAX) sh_atomic_min(&red->mn[4], v);
-      v = warp_max(mx4);
-      if (lane_id() == 0 && v != INT32_MIN) sh_atomic_max(&red->mx[4], v);
+    if (sp3.mn != INT32_MAX) {
+      sh_atomic_min(&red->mn[3], sp3.mn);
+      sh_atomic_max(&red->mx[3], sp3.mx);
+    }
+    if (sp4.mn != INT32_MAX) {
+      sh_atomic_min(&red->mn[4], sp4.mn);
+      sh_atomic_max(&red->mx[4], sp4.mx);
     }
   }
   cta_sync();
@@ -483,20 +573,38 @@ WFA_FN StepOut wf_step(Ctx& cx, const Dir& d, const Penalties& pen, int s) {
   const bool alloc[5] = {true, a_i1, a_i2, a_d1, a_d2};
   o.max_ak = red->max_ak;
   if (cx.tid == 0) {
+    bool nonempty[5];
     for (int c = 0; c < 5; ++c) {
       WfMeta m;
       m.lo = 1;
       m.hi = -1;
+      nonempty[c] = false;
       if (alloc[c]) {
         if (red->mn[c] <= red->mx[c]) {
           m.lo = red->mn[c];
           m.hi = red->mx[c];
+          nonempty[c] = true;
         } else {
           m.lo = 2;
           m.hi = -2;
         }
       }
       st.meta[slot5 + c] = m;
+    }
+    if (st.ub) {
+      // upper bounds of the max antidiagonal per row: exact for M (after extension); for the gap
+      // components ak(I/D[s][k]) = ak(source cell) + 1, so the bound follows the recurrence
+      const int ub_o1 = n_o1 ? UB_NONE : st.ub[st.slot(s_o1) * 5 + C_M];
+      const int ub_o2 = n_o2 ? UB_NONE : st.ub[st.slot(s_o2) * 5 + C_M];
+      const int ub_i1 = n_i1 ? UB_NONE : st.ub[st.slot(s_e1) * 5 + C_I1];
+      const int ub_d1 = n_d1 ? UB_NONE : st.ub[st.slot(s_e1) * 5 + C_D1];
+      const int ub_i2 = n_i2 ? UB_NONE : st.ub[st.slot(s_e2) * 5 + C_I2];
+      const int ub_d2 = n_d2 ? UB_NONE : st.ub[st.slot(s_e2) * 5 + C_D2];
+      st.ub[slot5 + C_M] = nonempty[C_M] ? red->max_ak : UB_NONE;
+      st.ub[slot5 + C_I1] = nonempty[C_I1] ? imax(ub_o1, ub_i1) + 1 : UB_NONE;
+      st.ub[slot5 + C_D1] = nonempty[C_D1] ? imax(ub_o1, ub_d1) + 1 : UB_NONE;
+      st.ub[slot5 + C_I2] = nonempty[C_I2] ? imax(ub_o2, ub_i2) + 1 : UB_NONE;
+      st.ub[slot5 + C_D2] = nonempty[C_D2] ? imax(ub_o2, ub_d2) + 1 : UB_NONE;
     }
     RedSlots* nx = &cx.sh->red[cx.parity ^ 1];
     for (int c = 0; c < 5; ++c) {
@@ -570,6 +678,9 @@ WFA_FN void wf_overlap(Ctx& cx, const Dir& d0, const Dir& d1, const Penalties& p
     bool run = score_i >= 0;
     const int gopen = (c == C_M) ? 0 : ((c == C_I1 || c == C_D1) ? pen.o1 : pen.o2);
     if (run && score_0 + score_i - gopen >= bp_score_in) run = false;
+    // h0 + h1 >= tlen  <=>  (2*h0 - k0) + (2*h1 - k1) >= plen + tlen: rows whose antidiagonal
+    // bounds cannot reach that are skipped without a scan (the scan would find nothing)
+    if (run && d0.st.ub[d0.st.slot(score_0) * 5 + c] + d1.st.ub[d1.st.slot(score_i) * 5 + c] < plen + tlen) run = false;
     if (run) {
       const WfMeta a = d0.st.get(score_0, c);
       const WfMeta b = d1.st.get(score_i, c);
@@ -659,6 +770,10 @@ WFA_FN int wf_find_breakpoint(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
                               unsigned long long* cells) {
   (void)cells;
   cta_sync();
+  df.st.cur_s = INT32_MIN / 2;
+  dr.st.cur_s = INT32_MIN / 2;
+  df.st.set_cur(0);
+  dr.st.set_cur(0);
   if (cx.tid == 0) {
     wf_init(df);
     wf_init(dr);
@@ -873,6 +988,7 @@ WFA_FN bool wf_backtrace(CtaShared* sh, const RunOut& ro, const WfStore& st, con
 // ---------------------------------------------------------------------------
 WFA_FN int wf_base(Ctx& cx, Dir& db, const Penalties& pen, const RunOut& ro) {
   cta_sync();
+  db.st.set_cur(0);
   if (cx.tid == 0) wf_init(db);
   red_reset(cx);
   int score = 0;
@@ -926,15 +1042,21 @@ struct PairResult {
 
 WFA_FN void set_dirs(Dir& df, Dir& dr, Dir& db, const SeqView& sv, const Frame& f) {
   const int plen = f.pe - f.pb, tlen = f.te - f.tb;
-  df.P = sv.p + f.pb;
-  df.T = sv.t + f.tb;
+  df.P = sv.p;
+  df.T = sv.t;
+  df.p0 = f.pb;
+  df.t0 = f.tb;
+  df.lbits = sv.lbits;
   df.plen = plen;
   df.tlen = tlen;
   df.reverse = 0;
   df.cbegin = f.cbegin;
   df.cend = f.cend;
-  dr.P = sv.p + f.pe - 1;
-  dr.T = sv.t + f.te - 1;
+  dr.P = sv.p;
+  dr.T = sv.t;
+  dr.p0 = f.pe - 1;
+  dr.t0 = f.te - 1;
+  dr.lbits = sv.lbits;
   dr.plen = plen;
   dr.tlen = tlen;
   dr.reverse = 1;
@@ -942,6 +1064,9 @@ WFA_FN void set_dirs(Dir& df, Dir& dr, Dir& db, const SeqView& sv, const Frame& 
   dr.cend = f.cbegin;
   db.P = df.P;
   db.T = df.T;
+  db.p0 = df.p0;
+  db.t0 = df.t0;
+  db.lbits = sv.lbits;
   db.plen = plen;
   db.tlen = tlen;
   db.reverse = 0;
@@ -959,15 +1084,22 @@ WFA_FN PairResult wf_align_pair(Ctx& cx, const SeqView& sv, int plen, int tlen, 
   Dir df, dr, db;
   df.st.base = ws.ring_f;
   df.st.meta = sh->meta_f;
+  df.st.ub = sh->ub_f;
   df.st.modular = 1;
   df.st.scope = pen.scope;
   df.st.W = ws.W;
   df.st.cap = 0;
+  df.st.cur_s = INT32_MIN / 2;
+  df.st.cur_slot = 0;
   dr.st = df.st;
   dr.st.base = ws.ring_r;
   dr.st.meta = sh->meta_r;
+  dr.st.ub = sh->ub_r;
   db.st.base = ws.full;
   db.st.meta = ws.full_meta;
+  db.st.ub = nullptr;
+  db.st.cur_s = 0;
+  db.st.cur_slot = 0;
   db.st.modular = 0;
   db.st.scope = pen.scope;
   db.st.W = 0;

@@ -8,16 +8,43 @@
 #include <vector>
 using namespace srb;
 
+// pack bytes at (1 << lbits) bits per symbol with a code table built from the bytes seen
+// (same layout as pack_kernel in kernels.cuh): returns the word array with 4 guard words each side
+struct Packer {
+  int code[256];
+  int n = 0;
+  Packer() { for (int i = 0; i < 256; ++i) code[i] = -1; }
+  void see(const char* s, int len) {
+    for (int i = 0; i < len; ++i) {
+      const unsigned char c = (unsigned char)s[i];
+      if (code[c] < 0) code[c] = n++;
+    }
+  }
+  int min_lbits() const { return n <= 4 ? 1 : n <= 16 ? 2 : 3; }
+  std::vector<uint32_t> pack(const char* s, int len, int lbits) const {
+    const int bits = 1 << lbits;
+    std::vector<uint32_t> w(((size_t)len * bits + 31) / 32 + 8, 0u);
+    for (int i = 0; i < len; ++i) {
+      const uint32_t c = lbits == 3 ? (unsigned char)s[i] : (uint32_t)code[(unsigned char)s[i]];
+      const size_t bit = (size_t)i * bits;
+      w[4 + bit / 32] |= c << (bit % 32);
+    }
+    return w;
+  }
+};
+
 extern "C" int emul_wfa_align(const char* pattern, int plen, const char* text, int tlen, int x, int o1, int e1, int o2,
-                              int e2, int W, int cap, char* cigar_out, int* cigar_len, int* score) {
+                              int e2, int W, int cap, int lbits, char* cigar_out, int* cigar_len, int* score) {
   Penalties pen{x, o1, e1, o2, e2, 0};
   int sc = o1 + e1 > o2 + e2 ? o1 + e1 : o2 + e2;
   if (x > sc) sc = x;
   pen.scope = sc + 1;
-  std::vector<uint8_t> pb(plen + 64, 0), tb(tlen + 64, 0);
-  memcpy(pb.data() + 32, pattern, plen);
-  memcpy(tb.data() + 32, text, tlen);
-  SeqView sv{pb.data() + 32, tb.data() + 32};
+  Packer pk;
+  pk.see(pattern, plen);
+  pk.see(text, tlen);
+  if (lbits <= 0 || lbits < pk.min_lbits()) lbits = pk.min_lbits();
+  std::vector<uint32_t> pb = pk.pack(pattern, plen, lbits), tb = pk.pack(text, tlen, lbits);
+  SeqView sv{pb.data() + 4, tb.data() + 4, lbits};
   std::vector<int32_t> rf((size_t)pen.scope * 5 * W), rr((size_t)pen.scope * 5 * W), full((size_t)5 * cap * cap);
   std::vector<WfMeta> fm((size_t)cap * 5);
   PairWorkspace ws{rf.data(), rr.data(), W, full.data(), fm.data(), cap};
@@ -42,16 +69,18 @@ extern "C" int emul_wfa_align(const char* pattern, int plen, const char* text, i
 }
 
 #include "../../seqrush_b200/csrc/orient_core.cuh"
-extern "C" int emul_orient(const char* pf, const char* pr, int plen, const char* text, int tlen, int* dist) {
-  std::vector<uint8_t> a(plen + 64, 0), b(plen + 64, 0), t(tlen + 64, 0);
-  memcpy(a.data() + 32, pf, plen);
-  memcpy(b.data() + 32, pr, plen);
-  memcpy(t.data() + 32, text, tlen);
+extern "C" int emul_orient(const char* pf, const char* pr, int plen, const char* text, int tlen, int lbits, int* dist) {
+  Packer pk;
+  pk.see(pf, plen);
+  pk.see(pr, plen);
+  pk.see(text, tlen);
+  if (lbits <= 0 || lbits < pk.min_lbits()) lbits = pk.min_lbits();
+  std::vector<uint32_t> a = pk.pack(pf, plen, lbits), b = pk.pack(pr, plen, lbits), t = pk.pack(text, tlen, lbits);
   const int stride = plen + tlen + 8;
   std::vector<int32_t> buf((size_t)4 * stride);
   CtaShared* sh = new CtaShared();
   Ctx cx{sh, 0, 1, 0};
-  OrientResult r = wf_orient(cx, a.data() + 32, b.data() + 32, t.data() + 32, plen, tlen, buf.data(), stride);
+  OrientResult r = wf_orient(cx, a.data() + 4, b.data() + 4, t.data() + 4, lbits, plen, tlen, buf.data(), stride);
   *dist = r.distance;
   delete sh;
   return r.is_reverse;

@@ -13,26 +13,27 @@ from conftest import ROOT, expand_rle, rle
 @pytest.fixture(scope="module")
 def emul(built):
     L = C.CDLL(os.path.join(ROOT, "tests", "host_emul", "libwfa_emul.so"))
-    L.emul_wfa_align.argtypes = [C.c_char_p, C.c_int, C.c_char_p, C.c_int] + [C.c_int] * 7 + [C.c_char_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
-    L.emul_orient.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, C.c_int, C.POINTER(C.c_int)]
+    L.emul_wfa_align.argtypes = [C.c_char_p, C.c_int, C.c_char_p, C.c_int] + [C.c_int] * 8 + [C.c_char_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.emul_orient.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_int)]
     return L
 
 
-def _align(L, p, t, pen, W=0, cap=0):
+def _align(L, p, t, pen, W=0, cap=0, lbits=0):
     W = W or 2 * (max(len(p), len(t)) + 8)
     W = (W + 63) & ~63
     cap = cap or max(512, 100 * pen[0] + 8) + 8
     buf = C.create_string_buffer(len(p) + len(t) + 16)
     n, sc = C.c_int(), C.c_int()
-    st = L.emul_wfa_align(p, len(p), t, len(t), *pen, W, cap, buf, C.byref(n), C.byref(sc))
+    st = L.emul_wfa_align(p, len(p), t, len(t), *pen, W, cap, lbits, buf, C.byref(n), C.byref(sc))
     return st, sc.value, buf.raw[:n.value]
 
 
 def test_emul_wfa2_goldens(emul, wfa2_golden):
     pen = tuple(wfa2_golden["penalties"][1:])
     for i, v in enumerate(wfa2_golden["vectors"]):
-        st, score, cig = _align(emul, v["p"].encode(), v["t"].encode(), pen)
-        assert st == 0 and rle(cig) == v["cigar"], i
+        for lbits in ((1, 2, 3) if i % 10 == 0 else (0,)):  # 2-, 4- and 8-bit packings must agree
+            st, score, cig = _align(emul, v["p"].encode(), v["t"].encode(), pen, lbits=lbits)
+            assert st == 0 and rle(cig) == v["cigar"], (i, lbits)
 
 
 def test_emul_seqrush_pairs(emul, seqrush_golden):
@@ -44,7 +45,7 @@ def test_emul_seqrush_pairs(emul, seqrush_golden):
             continue
         rc = reverse_complement(q)
         d = C.c_int()
-        is_rev = emul.emul_orient(q, rc, len(q), t, len(t), C.byref(d))
+        is_rev = emul.emul_orient(q, rc, len(q), t, len(t), 0, C.byref(d))
         assert is_rev == c["is_reverse"], c["tag"]
         assert d.value == min(c["fwd_ed"], c["rev_ed"]), c["tag"]
         st, score, cig = _align(emul, rc if is_rev else q, t, (5, 8, 2, 24, 1))
