@@ -8,6 +8,7 @@
 //   uf_* kernels   : BidirectedUnionFind entry points (src/bidirected_union_find.rs).
 #pragma once
 #include <cuda_runtime.h>
+#include <cstdio>
 #include "orient_core.cuh"
 
 namespace srb {
@@ -162,6 +163,11 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
   const bool staged = a.smem_seq_words != 0;
   uint32_t phase = 0;
   if (staged && threadIdx.x == 0) mbar_init(&s_bar, 1);
+#ifdef WFA_PROFILE
+  if (threadIdx.x == 0)
+    for (int i = 0; i < 16; ++i) sh.prof[i] = 0;
+  const long long prof_start = clock64();
+#endif
   while (true) {
     __syncthreads();
     if (threadIdx.x == 0) s_pair = atomicAdd(a.next_pair, 1u);
@@ -277,6 +283,18 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
       a.out[pi] = o;
     }
   }
+#ifdef WFA_PROFILE
+  if (threadIdx.x == 0 && blockIdx.x < 4) {
+    const unsigned long long* pf = sh.prof;
+    const double n = pf[0] ? (double)pf[0] : 1.0;
+    printf("[prof cta %d] ring steps %llu  total cyc %lld | per step: top-barrier %.0f  setup %.0f  loop %.0f  finish %.0f  "
+           "| avg width %.0f\n",
+           (int)blockIdx.x, pf[0], clock64() - prof_start, pf[1] / n, pf[2] / n, pf[3] / n, pf[4] / n, pf[7] / n);
+    printf("[prof cta %d] warp1 interior chunks %llu: compute %.0f cyc, extend %.0f cyc | warp0 fringe chunks %llu: %.0f cyc\n",
+           (int)blockIdx.x, pf[8], pf[9] / (pf[8] ? (double)pf[8] : 1.0), pf[10] / (pf[8] ? (double)pf[8] : 1.0), pf[11],
+           pf[12] / (pf[11] ? (double)pf[11] : 1.0));
+  }
+#endif
 }
 
 // ---------------------------------------------------------------------------

@@ -120,20 +120,14 @@ struct WfStore {
     const int t = cur_slot - (cur_s - s);
     return t < 0 ? t + scope : t;
   }
-  WFA_FN int32_t* row_of_slot(int sl, int c) const { return base + ((size_t)(sl * 5 + c)) * (size_t)W + (W >> 1); }
+  WFA_FN int32_t* row_of_slot(int sl, int c) const { return base + (uint32_t)((sl * 5 + c) * W + (W >> 1)); }
   WFA_FN int32_t* row(int s, int c) const {
     if (modular) return row_of_slot(slot(s), c);
     return base + (size_t)c * (size_t)cap * (size_t)cap + (size_t)s * (size_t)s + s;
   }
   WFA_FN WfMeta get(int s, int c) const {
-    WfMeta m;
-    if (s < 0) {
-      m.lo = 1;
-      m.hi = -1;
-      return m;
-    }
-    m = meta[slot(s) * 5 + c];
-    if (m.lo > m.hi) {
+    WfMeta m = meta[slot(s < 0 ? cur_s : s) * 5 + c];
+    if (s < 0 || m.lo > m.hi) {
       m.lo = 1;
       m.hi = -1;
     }
@@ -171,6 +165,9 @@ struct CtaShared {
   // work counters (roofline accounting)
   unsigned long long cells;   // BiWFA cells: one diagonal at one score, all five components
   unsigned long long ocells;  // orientation (unit-cost) cells
+#ifdef WFA_PROFILE
+  unsigned long long prof[16];  // cycle counters of thread 0 (development only)
+#endif
 };
 
 struct Ctx {
@@ -285,7 +282,13 @@ struct Dir {
   int cbegin, cend;
 };
 
-WFA_FN int32_t rd(const int32_t* row, WfMeta m, int k) { return (k >= m.lo && k <= m.hi) ? row[k] : OFFSET_NULL; }
+// checked read without a branch: the load is always issued (diagonal 0 of every row lies inside the
+// allocation), so the reads of a fringe chunk overlap instead of paying one memory latency each
+WFA_FN int32_t rd(const int32_t* row, WfMeta m, int k) {
+  const bool ok = (k >= m.lo) & (k <= m.hi);
+  const int32_t v = row[ok ? k : 0];
+  return ok ? v : OFFSET_NULL;
+}
 
 // ---------------------------------------------------------------------------
 // Initial wavefront (WFA/wavefront_aligner.c:252-383, end-to-end form only).
@@ -387,6 +390,116 @@ struct Span {
 
 WFA_FN bool in_bounds(int32_t h, int k, uint32_t tlen, uint32_t plen) {
   return (uint32_t)h <= tlen && (uint32_t)(h - k) <= plen;
+}
+
+// ---------------------------------------------------------------------------
+// Tail of a score step, shared by the scalar and the vector step: merge the per-warp trims
+// (lanes 0..10 of every warp issue one shared-memory atomic each), publish the five metas and
+// antidiagonal bounds (one lane per component), reset the other reduction buffer, end test.
+// ---------------------------------------------------------------------------
+struct StepCtl {
+  int s, slot5;
+  int s_o1, s_e1, s_o2, s_e2;
+  bool n_o1, n_o2, n_i1, n_d1, n_i2, n_d2;
+  bool a_i1, a_i2, a_d1, a_d2;
+};
+
+WFA_FN void publish_comp(const WfStore& st, const RedSlots* red, const StepCtl& t, int c) {
+  const bool al = c == C_M ? true : c == C_I1 ? t.a_i1 : c == C_I2 ? t.a_i2 : c == C_D1 ? t.a_d1 : t.a_d2;
+  WfMeta m;
+  m.lo = 1;
+  m.hi = -1;
+  bool nonempty = false;
+  if (al) {
+    if (red->mn[c] <= red->mx[c]) {
+      m.lo = red->mn[c];
+      m.hi = red->mx[c];
+      nonempty = true;
+    } else {
+      m.lo = 2;
+      m.hi = -2;
+    }
+  }
+  st.meta[t.slot5 + c] = m;
+  if (st.ub) {
+    // exact for M (after extension); for the gap components ak(I/D[s][k]) = ak(source cell) + 1
+    int u = UB_NONE;
+    if (nonempty) {
+      if (c == C_M) {
+        u = red->max_ak;
+      } else {
+        const bool one = (c == C_I1 || c == C_D1);
+        const bool n_m = one ? t.n_o1 : t.n_o2;
+        const bool n_s = c == C_I1 ? t.n_i1 : c == C_I2 ? t.n_i2 : c == C_D1 ? t.n_d1 : t.n_d2;
+        const int ua = n_m ? UB_NONE : st.ub[st.slot(one ? t.s_o1 : t.s_o2) * 5 + C_M];
+        const int ub = n_s ? UB_NONE : st.ub[st.slot(one ? t.s_e1 : t.s_e2) * 5 + c];
+        u = imax(ua, ub) + 1;
+      }
+    }
+    st.ub[t.slot5 + c] = u;
+  }
+}
+
+WFA_FN void step_finish(Ctx& cx, const Dir& d, const StepCtl& t, const int* mn, const int* mx, int max_ak, StepOut& o) {
+  const WfStore& st = d.st;
+  RedSlots* red = &cx.sh->red[cx.parity];
+  max_ak = warp_max(max_ak);
+#if WFA_DEVICE
+  {
+    const int lane = lane_id();
+    int v = max_ak;
+    v = lane == 0 ? mn[0] : lane == 1 ? mn[1] : lane == 2 ? mn[2] : lane == 3 ? mn[3] : lane == 4 ? mn[4] : v;
+    v = lane == 5 ? mx[0] : lane == 6 ? mx[1] : lane == 7 ? mx[2] : lane == 8 ? mx[3] : lane == 9 ? mx[4] : v;
+    int* slot = &red->mn[0] + lane;  // RedSlots = mn[5], mx[5], max_ak: eleven consecutive ints
+    if (lane < 5) {
+      if (v != INT32_MAX) atomicMin(slot, v);
+    } else if (lane < 10) {
+      if (v != INT32_MIN) atomicMax(slot, v);
+    } else if (lane == 10) {
+      if (v > 0) atomicMax(slot, v);
+    }
+  }
+#else
+  if (max_ak > 0) sh_atomic_max(&red->max_ak, max_ak);
+  for (int c = 0; c < 5; ++c) {
+    if (mn[c] != INT32_MAX) {
+      sh_atomic_min(&red->mn[c], mn[c]);
+      sh_atomic_max(&red->mx[c], mx[c]);
+    }
+  }
+#endif
+  cta_sync();
+  o.max_ak = red->max_ak;
+#if WFA_DEVICE
+  if (cx.tid < 5) {
+    publish_comp(st, red, t, cx.tid);
+  } else if (cx.tid < 16) {
+    int* nx = &cx.sh->red[cx.parity ^ 1].mn[0];
+    const int i = cx.tid - 5;
+    nx[i] = i < 5 ? INT32_MAX : i < 10 ? INT32_MIN : 0;
+  }
+#else
+  for (int c = 0; c < 5; ++c) publish_comp(st, red, t, c);
+  {
+    RedSlots* nx = &cx.sh->red[cx.parity ^ 1];
+    for (int c = 0; c < 5; ++c) {
+      nx->mn[c] = INT32_MAX;
+      nx->mx[c] = INT32_MIN;
+    }
+    nx->max_ak = 0;
+  }
+#endif
+  // termination (WFA/wavefront_termination.c:37-113): read directly from the reduction slots / rows
+  {
+    const int ak = d.tlen - d.plen;
+    const int ce = d.cend;
+    const bool al = ce == C_M ? true : ce == C_I1 ? t.a_i1 : ce == C_I2 ? t.a_i2 : ce == C_D1 ? t.a_d1 : t.a_d2;
+    const bool present = al && red->mn[ce] <= red->mx[ce];
+    if (present && red->mn[ce] <= ak && ak <= red->mx[ce]) {
+      if (st.row(t.s, ce)[ak] >= d.tlen) o.end_reached = 1;
+    }
+  }
+  cx.parity ^= 1;
 }
 
 // ---------------------------------------------------------------------------
@@ -543,86 +656,430 @@ WFA_FN StepOut wf_step(Ctx& cx, Dir& d, const Penalties& pen, int s) {
     if (act) w_m[k] = mx;
   }
   // merge the per-warp trims (WFA/wavefront_compute.c:579-611 does the same with two linear scans)
-  RedSlots* red = &cx.sh->red[cx.parity];
-  max_ak = warp_max(max_ak);
-  if (lane == 0) {
-    if (max_ak > 0) sh_atomic_max(&red->max_ak, max_ak);
-    if (sp0.mn != INT32_MAX) {
-      sh_atomic_min(&red->mn[0], sp0.mn);
-      sh_atomic_max(&red->mx[0], sp0.mx);
+  StepCtl ctl;
+  ctl.s = s;
+  ctl.slot5 = slot5;
+  ctl.s_o1 = s_o1;
+  ctl.s_e1 = s_e1;
+  ctl.s_o2 = s_o2;
+  ctl.s_e2 = s_e2;
+  ctl.n_o1 = n_o1;
+  ctl.n_o2 = n_o2;
+  ctl.n_i1 = n_i1;
+  ctl.n_d1 = n_d1;
+  ctl.n_i2 = n_i2;
+  ctl.n_d2 = n_d2;
+  ctl.a_i1 = a_i1;
+  ctl.a_i2 = a_i2;
+  ctl.a_d1 = a_d1;
+  ctl.a_d2 = a_d2;
+  const int mns[5] = {sp0.mn, sp1.mn, sp2.mn, sp3.mn, sp4.mn};
+  const int mxs[5] = {sp0.mx, sp1.mx, sp2.mx, sp3.mx, sp4.mx};
+  step_finish(cx, d, ctl, mns, mxs, max_ak, o);
+  return o;
+}
+
+// ---------------------------------------------------------------------------
+// Vectorised score step for the modular rings (the breakpoint searches, where
+// almost all cells are computed). Same decisions as wf_step; the layout is four
+// consecutive diagonals per lane, 128 per warp chunk, chunk starts aligned to 4
+// so that every ring row is read and written with 128-bit accesses; the k-1 /
+// k+1 neighbours come from the adjacent lanes by shuffle (one scalar load at
+// each chunk edge). Interior chunks need no range checks. The in-bounds test of
+// the four gap components uses M: M = max of the five, so M in bounds bounds
+// them from above and only `value >= max(0,k)` is left to check; one vote per
+// chunk then covers all trims when everything is in bounds (the common case).
+// ---------------------------------------------------------------------------
+#if WFA_DEVICE
+WFA_FN int32_t shfl_up1(int32_t v) { return __shfl_up_sync(0xffffffffu, v, 1); }
+WFA_FN int32_t shfl_down1(int32_t v) { return __shfl_down_sync(0xffffffffu, v, 1); }
+WFA_FN bool warp_all(bool p) { return __all_sync(0xffffffffu, p); }
+#else
+WFA_FN int32_t shfl_up1(int32_t v) { return v; }
+WFA_FN int32_t shfl_down1(int32_t v) { return v; }
+WFA_FN bool warp_all(bool p) { return p; }
+#endif
+
+#ifdef WFA_PROFILE
+#define PROF_T(v) const long long v = clock64()
+#else
+#define PROF_T(v)
+#endif
+
+struct I4 {
+  int32_t x, y, z, w;
+};
+WFA_FN I4 ld4(const int32_t* p) {
+#if WFA_DEVICE
+  const int4 v = *reinterpret_cast<const int4*>(p);
+  I4 r;
+  r.x = v.x;
+  r.y = v.y;
+  r.z = v.z;
+  r.w = v.w;
+  return r;
+#else
+  I4 r;
+  r.x = p[0];
+  r.y = p[1];
+  r.z = p[2];
+  r.w = p[3];
+  return r;
+#endif
+}
+WFA_FN void st4(int32_t* p, int32_t a, int32_t b, int32_t c, int32_t e) {
+#if WFA_DEVICE
+  *reinterpret_cast<int4*>(p) = make_int4(a, b, c, e);
+#else
+  p[0] = a;
+  p[1] = b;
+  p[2] = c;
+  p[3] = e;
+#endif
+}
+
+// first/last valid diagonal of one component inside a chunk where lane l holds diagonals kb+4l+j
+struct Span4 {
+  int mn, mx;
+  WFA_FN void init() {
+    mn = INT32_MAX;
+    mx = INT32_MIN;
+  }
+  WFA_FN void add_full(int kb, int n) {
+    mn = imin(mn, kb);
+    mx = imax(mx, kb + n - 1);
+  }
+  WFA_FN void add(bool p0, bool p1, bool p2, bool p3, int kb) {
+    const uint32_t b0 = warp_ballot(p0), b1 = warp_ballot(p1), b2 = warp_ballot(p2), b3 = warp_ballot(p3);
+    if (b0) {
+      mn = imin(mn, kb + 4 * ctz32(b0));
+      mx = imax(mx, kb + 4 * (31 - clz32(b0)));
     }
-    if (sp1.mn != INT32_MAX) {
-      sh_atomic_min(&red->mn[1], sp1.mn);
-      sh_atomic_max(&red->mx[1], sp1.mx);
+    if (b1) {
+      mn = imin(mn, kb + 4 * ctz32(b1) + 1);
+      mx = imax(mx, kb + 4 * (31 - clz32(b1)) + 1);
     }
-    if (sp2.mn != INT32_MAX) {
-      sh_atomic_min(&red->mn[2], sp2.mn);
-      sh_atomic_max(&red->mx[2], sp2.mx);
+    if (b2) {
+      mn = imin(mn, kb + 4 * ctz32(b2) + 2);
+      mx = imax(mx, kb + 4 * (31 - clz32(b2)) + 2);
     }
-    if (sp3.mn != INT32_MAX) {
-      sh_atomic_min(&red->mn[3], sp3.mn);
-      sh_atomic_max(&red->mx[3], sp3.mx);
-    }
-    if (sp4.mn != INT32_MAX) {
-      sh_atomic_min(&red->mn[4], sp4.mn);
-      sh_atomic_max(&red->mx[4], sp4.mx);
+    if (b3) {
+      mn = imin(mn, kb + 4 * ctz32(b3) + 3);
+      mx = imax(mx, kb + 4 * (31 - clz32(b3)) + 3);
     }
   }
+};
+
+template <bool REV>
+WFA_FN int wf_extend_cell_t(const Dir& d, int k, int32_t off) {
+  const int v = off - k, h = off;
+  const int room = imin(d.plen - v, d.tlen - h);
+  if (!REV) return off + lcp_fwd(d.P, d.T, d.p0 + v, d.t0 + h, room, d.lbits);
+  return off + lcp_rev(d.P, d.T, d.p0 - v, d.t0 - h, room, d.lbits);
+}
+
+template <bool REV>
+WFA_FN StepOut wf_step_vec(Ctx& cx, Dir& d, const Penalties& pen, int s) {
+  StepOut o;
+  o.null_step = 0;
+  o.end_reached = 0;
+  o.max_ak = 0;
+  o.overflow = 0;
+  d.st.set_cur(s);
+  PROF_T(t0);
   cta_sync();
-  // publish metas; reset the other reduction buffer for the next step
-  const bool alloc[5] = {true, a_i1, a_i2, a_d1, a_d2};
-  o.max_ak = red->max_ak;
-  if (cx.tid == 0) {
-    bool nonempty[5];
-    for (int c = 0; c < 5; ++c) {
-      WfMeta m;
-      m.lo = 1;
-      m.hi = -1;
-      nonempty[c] = false;
-      if (alloc[c]) {
-        if (red->mn[c] <= red->mx[c]) {
-          m.lo = red->mn[c];
-          m.hi = red->mx[c];
-          nonempty[c] = true;
+  PROF_T(t1);
+  const WfStore& st = d.st;
+  const int s_mis = s - pen.x, s_o1 = s - pen.o1 - pen.e1, s_e1 = s - pen.e1;
+  const int s_o2 = s - pen.o2 - pen.e2, s_e2 = s - pen.e2;
+  const WfMeta m_mis = st.get(s_mis, C_M), m_o1 = st.get(s_o1, C_M), m_o2 = st.get(s_o2, C_M);
+  const WfMeta m_i1 = st.get(s_e1, C_I1), m_d1 = st.get(s_e1, C_D1);
+  const WfMeta m_i2 = st.get(s_e2, C_I2), m_d2 = st.get(s_e2, C_D2);
+  const bool n_mis = m_mis.lo > m_mis.hi, n_o1 = m_o1.lo > m_o1.hi, n_o2 = m_o2.lo > m_o2.hi;
+  const bool n_i1 = m_i1.lo > m_i1.hi, n_d1 = m_d1.lo > m_d1.hi, n_i2 = m_i2.lo > m_i2.hi, n_d2 = m_d2.lo > m_d2.hi;
+  const int slot5 = st.slot(s) * 5;
+  if (n_mis && n_o1 && n_o2 && n_i1 && n_d1 && n_i2 && n_d2) {
+    if (cx.tid == 0) {
+      for (int c = 0; c < 5; ++c) {
+        st.meta[slot5 + c].lo = 1;
+        st.meta[slot5 + c].hi = -1;
+        st.ub[slot5 + c] = UB_NONE;
+      }
+    }
+    o.null_step = 1;
+    return o;
+  }
+  int lo = m_mis.lo, hi = m_mis.hi;
+  lo = imin(lo, m_o1.lo - 1);
+  hi = imax(hi, m_o1.hi + 1);
+  lo = imin(lo, m_i1.lo + 1);
+  hi = imax(hi, m_i1.hi + 1);
+  lo = imin(lo, m_d1.lo - 1);
+  hi = imax(hi, m_d1.hi - 1);
+  lo = imin(lo, m_o2.lo - 1);
+  hi = imax(hi, m_o2.hi + 1);
+  lo = imin(lo, m_i2.lo + 1);
+  hi = imax(hi, m_i2.hi + 1);
+  lo = imin(lo, m_d2.lo - 1);
+  hi = imax(hi, m_d2.hi - 1);
+  // keep 8 diagonals of slack on both sides: aligned 4-wide accesses may touch [lo-3, hi+3]
+  if (lo <= -(st.W >> 1) + 8 || hi >= (st.W >> 1) - 8) {
+    o.overflow = 1;
+    return o;
+  }
+  if (cx.tid == 0) cx.sh->cells += (unsigned long long)(hi - lo + 1);
+  const bool a_i1 = !n_o1 || !n_i1, a_d1 = !n_o1 || !n_d1, a_i2 = !n_o2 || !n_i2, a_d2 = !n_o2 || !n_d2;
+  int in_lo = 1, in_hi = 0;
+  if (!(n_mis || n_o1 || n_o2 || n_i1 || n_d1 || n_i2 || n_d2)) {
+    in_lo = imax(imax(m_mis.lo, imax(m_o1.lo, m_o2.lo) + 1), imax(imax(m_i1.lo, m_i2.lo) + 1, imax(m_d1.lo, m_d2.lo) - 1));
+    in_hi = imin(imin(m_mis.hi, imin(m_o1.hi, m_o2.hi) - 1), imin(imin(m_i1.hi, m_i2.hi) + 1, imin(m_d1.hi, m_d2.hi) - 1));
+    in_lo = imax(in_lo, lo);
+    in_hi = imin(in_hi, hi);
+  }
+  const int32_t* r_mis = st.row(s_mis < 0 ? 0 : s_mis, C_M);
+  const int32_t* r_o1 = st.row(s_o1 < 0 ? 0 : s_o1, C_M);
+  const int32_t* r_o2 = st.row(s_o2 < 0 ? 0 : s_o2, C_M);
+  const int32_t* r_i1 = st.row(s_e1 < 0 ? 0 : s_e1, C_I1);
+  const int32_t* r_d1 = st.row(s_e1 < 0 ? 0 : s_e1, C_D1);
+  const int32_t* r_i2 = st.row(s_e2 < 0 ? 0 : s_e2, C_I2);
+  const int32_t* r_d2 = st.row(s_e2 < 0 ? 0 : s_e2, C_D2);
+  int32_t* w_m = st.row(s, C_M);
+  int32_t* w_i1 = st.row(s, C_I1);
+  int32_t* w_i2 = st.row(s, C_I2);
+  int32_t* w_d1 = st.row(s, C_D1);
+  int32_t* w_d2 = st.row(s, C_D2);
+  const uint32_t tlen = (uint32_t)d.tlen, plen = (uint32_t)d.plen;
+  Span4 sp0, sp1, sp2, sp3, sp4;
+  sp0.init();
+  sp1.init();
+  sp2.init();
+  sp3.init();
+  sp4.init();
+  int max_ak = 0;
+  const int lane = lane_id();
+#if WFA_DEVICE
+  const int warp = cx.tid >> 5, nwarps = cx.nt >> 5;
+#else
+  const int warp = 0, nwarps = 1;
+#endif
+  constexpr int CH = LANES * 4;
+  PROF_T(t2);
+  const int lo_al = lo & ~3;  // arithmetic: rounds towards -inf on two's complement
+  for (int kb = lo_al + warp * CH; kb <= hi; kb += nwarps * CH) {
+    const int k0 = kb + 4 * lane;
+    int32_t ins1[4], ins2[4], del1[4], del2[4], mx[4];
+    bool vm[4];
+    PROF_T(tc0);
+    // 128-bit reads of the seven source rows (always inside the row allocation: rows keep >= 8
+    // diagonals of slack beyond [lo, hi]); neighbours k0-1 / k0+4 by shuffle, chunk edges by a load
+    // lanes of the last chunk that lie wholly beyond hi neither load nor store (they would leave
+    // the row); kq is a safe stand-in address for them
+    const bool lane_act = k0 <= hi;
+    const int kq = lane_act ? k0 : lo_al;
+    I4 vo1 = ld4(r_o1 + kq), vo2 = ld4(r_o2 + kq), vi1 = ld4(r_i1 + kq), vi2 = ld4(r_i2 + kq);
+    I4 vd1 = ld4(r_d1 + kq), vd2 = ld4(r_d2 + kq), vmis = ld4(r_mis + kq);
+    int32_t o1L = shfl_up1(vo1.w), o2L = shfl_up1(vo2.w), i1L = shfl_up1(vi1.w), i2L = shfl_up1(vi2.w);
+    int32_t o1R = shfl_down1(vo1.x), o2R = shfl_down1(vo2.x), d1R = shfl_down1(vd1.x), d2R = shfl_down1(vd2.x);
+    if (lane == 0) {
+      o1L = r_o1[kq - 1];
+      o2L = r_o2[kq - 1];
+      i1L = r_i1[kq - 1];
+      i2L = r_i2[kq - 1];
+    }
+    if (lane == LANES - 1) {
+      o1R = r_o1[kq + 4];
+      o2R = r_o2[kq + 4];
+      d1R = r_d1[kq + 4];
+      d2R = r_d2[kq + 4];
+    }
+    const bool interior = kb >= in_lo && kb + CH - 1 <= in_hi;  // warp-uniform
+    if (!interior) {
+      // fringe chunk: whatever lies outside its source wavefront reads as NULL
+      // (WFA/wavefront_compute.c:251-295 pads the same way)
+#define MSK(v, m, kk) v = ((kk) >= (m).lo && (kk) <= (m).hi) ? v : OFFSET_NULL
+      MSK(o1L, m_o1, k0 - 1);
+      MSK(vo1.x, m_o1, k0);
+      MSK(vo1.y, m_o1, k0 + 1);
+      MSK(vo1.z, m_o1, k0 + 2);
+      MSK(vo1.w, m_o1, k0 + 3);
+      MSK(o1R, m_o1, k0 + 4);
+      MSK(o2L, m_o2, k0 - 1);
+      MSK(vo2.x, m_o2, k0);
+      MSK(vo2.y, m_o2, k0 + 1);
+      MSK(vo2.z, m_o2, k0 + 2);
+      MSK(vo2.w, m_o2, k0 + 3);
+      MSK(o2R, m_o2, k0 + 4);
+      MSK(i1L, m_i1, k0 - 1);
+      MSK(vi1.x, m_i1, k0);
+      MSK(vi1.y, m_i1, k0 + 1);
+      MSK(vi1.z, m_i1, k0 + 2);
+      MSK(i2L, m_i2, k0 - 1);
+      MSK(vi2.x, m_i2, k0);
+      MSK(vi2.y, m_i2, k0 + 1);
+      MSK(vi2.z, m_i2, k0 + 2);
+      MSK(vd1.y, m_d1, k0 + 1);
+      MSK(vd1.z, m_d1, k0 + 2);
+      MSK(vd1.w, m_d1, k0 + 3);
+      MSK(d1R, m_d1, k0 + 4);
+      MSK(vd2.y, m_d2, k0 + 1);
+      MSK(vd2.z, m_d2, k0 + 2);
+      MSK(vd2.w, m_d2, k0 + 3);
+      MSK(d2R, m_d2, k0 + 4);
+      MSK(vmis.x, m_mis, k0);
+      MSK(vmis.y, m_mis, k0 + 1);
+      MSK(vmis.z, m_mis, k0 + 2);
+      MSK(vmis.w, m_mis, k0 + 3);
+#undef MSK
+    }
+    ins1[0] = imax(o1L, i1L) + 1;
+    ins1[1] = imax(vo1.x, vi1.x) + 1;
+    ins1[2] = imax(vo1.y, vi1.y) + 1;
+    ins1[3] = imax(vo1.z, vi1.z) + 1;
+    ins2[0] = imax(o2L, i2L) + 1;
+    ins2[1] = imax(vo2.x, vi2.x) + 1;
+    ins2[2] = imax(vo2.y, vi2.y) + 1;
+    ins2[3] = imax(vo2.z, vi2.z) + 1;
+    del1[0] = imax(vo1.y, vd1.y);
+    del1[1] = imax(vo1.z, vd1.z);
+    del1[2] = imax(vo1.w, vd1.w);
+    del1[3] = imax(o1R, d1R);
+    del2[0] = imax(vo2.y, vd2.y);
+    del2[1] = imax(vo2.z, vd2.z);
+    del2[2] = imax(vo2.w, vd2.w);
+    del2[3] = imax(o2R, d2R);
+    const int32_t mis[4] = {vmis.x + 1, vmis.y + 1, vmis.z + 1, vmis.w + 1};
+    bool all_ok = true;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int k = k0 + j;
+      int32_t m5 = imax(imax(del1[j], del2[j]), imax(mis[j], imax(ins1[j], ins2[j])));
+      vm[j] = in_bounds(m5, k, tlen, plen) && (interior || (k >= lo && k <= hi));
+      if (!vm[j]) m5 = OFFSET_NULL;
+      mx[j] = m5;
+      const int32_t low = imin(imin(ins1[j], ins2[j]), imin(del1[j], del2[j]));
+      all_ok = all_ok && vm[j] && low >= imax(0, k);
+    }
+    // gap components of this score (rows of components that are not allocated this step are never
+    // read: their meta says absent)
+    if (lane_act) {
+      st4(w_i1 + k0, ins1[0], ins1[1], ins1[2], ins1[3]);
+      st4(w_i2 + k0, ins2[0], ins2[1], ins2[2], ins2[3]);
+      st4(w_d1 + k0, del1[0], del1[1], del1[2], del1[3]);
+      st4(w_d2 + k0, del2[0], del2[1], del2[2], del2[3]);
+    }
+    if (warp_all(all_ok)) {
+      // every cell of the chunk is in bounds in all five components (then all are allocated too)
+      sp0.add_full(kb, CH);
+      sp1.add_full(kb, CH);
+      sp2.add_full(kb, CH);
+      sp3.add_full(kb, CH);
+      sp4.add_full(kb, CH);
+    } else {
+      bool a0 = true, a1 = true, a2 = true, a3 = true;
+      if (!interior) {
+        a0 = k0 >= lo && k0 <= hi;
+        a1 = k0 + 1 >= lo && k0 + 1 <= hi;
+        a2 = k0 + 2 >= lo && k0 + 2 <= hi;
+        a3 = k0 + 3 >= lo && k0 + 3 <= hi;
+      }
+      sp0.add(vm[0], vm[1], vm[2], vm[3], kb);
+      if (a_i1)
+        sp1.add(a0 && in_bounds(ins1[0], k0, tlen, plen), a1 && in_bounds(ins1[1], k0 + 1, tlen, plen),
+                a2 && in_bounds(ins1[2], k0 + 2, tlen, plen), a3 && in_bounds(ins1[3], k0 + 3, tlen, plen), kb);
+      if (a_i2)
+        sp2.add(a0 && in_bounds(ins2[0], k0, tlen, plen), a1 && in_bounds(ins2[1], k0 + 1, tlen, plen),
+                a2 && in_bounds(ins2[2], k0 + 2, tlen, plen), a3 && in_bounds(ins2[3], k0 + 3, tlen, plen), kb);
+      if (a_d1)
+        sp3.add(a0 && in_bounds(del1[0], k0, tlen, plen), a1 && in_bounds(del1[1], k0 + 1, tlen, plen),
+                a2 && in_bounds(del1[2], k0 + 2, tlen, plen), a3 && in_bounds(del1[3], k0 + 3, tlen, plen), kb);
+      if (a_d2)
+        sp4.add(a0 && in_bounds(del2[0], k0, tlen, plen), a1 && in_bounds(del2[1], k0 + 1, tlen, plen),
+                a2 && in_bounds(del2[2], k0 + 2, tlen, plen), a3 && in_bounds(del2[3], k0 + 3, tlen, plen), kb);
+    }
+    PROF_T(tc1);
+    // exact-match extension of the four M cells: the first packed window of all four is compared
+    // together (independent loads overlap); only cells whose whole window matched take the loop
+    {
+      uint32_t xw[4];
+      int room[4];
+      const int per = 32 >> d.lbits;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int h = vm[j] ? mx[j] : 0, v = vm[j] ? mx[j] - (k0 + j) : 0;
+        room[j] = vm[j] ? imin(d.plen - v, d.tlen - h) : 0;
+        if (!REV) {
+          xw[j] = pk_window_fwd(d.P, d.p0 + v, d.lbits) ^ pk_window_fwd(d.T, d.t0 + h, d.lbits);
         } else {
-          m.lo = 2;
-          m.hi = -2;
+          xw[j] = pk_window_rev(d.P, d.p0 - v, d.lbits) ^ pk_window_rev(d.T, d.t0 - h, d.lbits);
         }
       }
-      st.meta[slot5 + c] = m;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (vm[j]) {
+          int n;
+          if (xw[j]) {
+            n = (REV ? clz32(xw[j]) : ctz32(xw[j])) >> d.lbits;
+          } else {
+            n = per;
+            if (n < room[j]) {
+              const int h = mx[j] + n, v = mx[j] - (k0 + j) + n;
+              n += REV ? lcp_rev(d.P, d.T, d.p0 - v, d.t0 - h, room[j] - n, d.lbits)
+                       : lcp_fwd(d.P, d.T, d.p0 + v, d.t0 + h, room[j] - n, d.lbits);
+            }
+          }
+          mx[j] += imin(n, room[j]);
+          max_ak = imax(max_ak, 2 * mx[j] - (k0 + j));
+        }
+      }
     }
-    if (st.ub) {
-      // upper bounds of the max antidiagonal per row: exact for M (after extension); for the gap
-      // components ak(I/D[s][k]) = ak(source cell) + 1, so the bound follows the recurrence
-      const int ub_o1 = n_o1 ? UB_NONE : st.ub[st.slot(s_o1) * 5 + C_M];
-      const int ub_o2 = n_o2 ? UB_NONE : st.ub[st.slot(s_o2) * 5 + C_M];
-      const int ub_i1 = n_i1 ? UB_NONE : st.ub[st.slot(s_e1) * 5 + C_I1];
-      const int ub_d1 = n_d1 ? UB_NONE : st.ub[st.slot(s_e1) * 5 + C_D1];
-      const int ub_i2 = n_i2 ? UB_NONE : st.ub[st.slot(s_e2) * 5 + C_I2];
-      const int ub_d2 = n_d2 ? UB_NONE : st.ub[st.slot(s_e2) * 5 + C_D2];
-      st.ub[slot5 + C_M] = nonempty[C_M] ? red->max_ak : UB_NONE;
-      st.ub[slot5 + C_I1] = nonempty[C_I1] ? imax(ub_o1, ub_i1) + 1 : UB_NONE;
-      st.ub[slot5 + C_D1] = nonempty[C_D1] ? imax(ub_o1, ub_d1) + 1 : UB_NONE;
-      st.ub[slot5 + C_I2] = nonempty[C_I2] ? imax(ub_o2, ub_i2) + 1 : UB_NONE;
-      st.ub[slot5 + C_D2] = nonempty[C_D2] ? imax(ub_o2, ub_d2) + 1 : UB_NONE;
+    if (lane_act) st4(w_m + k0, mx[0], mx[1], mx[2], mx[3]);
+#ifdef WFA_PROFILE
+    if (cx.tid == 32 && interior) {
+      const long long tc2 = clock64();
+      cx.sh->prof[8] += 1;
+      cx.sh->prof[9] += tc1 - tc0;
+      cx.sh->prof[10] += tc2 - tc1;
     }
-    RedSlots* nx = &cx.sh->red[cx.parity ^ 1];
-    for (int c = 0; c < 5; ++c) {
-      nx->mn[c] = INT32_MAX;
-      nx->mx[c] = INT32_MIN;
+    if (cx.tid == 0 && !interior) {
+      cx.sh->prof[11] += 1;
+      cx.sh->prof[12] += clock64() - tc0;
     }
-    nx->max_ak = 0;
+#endif
   }
-  // termination (WFA/wavefront_termination.c:37-113): read directly from the reduction slots / rows
-  {
-    const int ak = d.tlen - d.plen;
-    const int ce = d.cend;
-    const bool present = alloc[ce] && red->mn[ce] <= red->mx[ce];
-    if (present && red->mn[ce] <= ak && ak <= red->mx[ce]) {
-      if (st.row(s, ce)[ak] >= d.tlen) o.end_reached = 1;
-    }
+  // merge the per-warp trims, publish metas and antidiagonal bounds (as in wf_step)
+  PROF_T(t3);
+  StepCtl ctl;
+  ctl.s = s;
+  ctl.slot5 = slot5;
+  ctl.s_o1 = s_o1;
+  ctl.s_e1 = s_e1;
+  ctl.s_o2 = s_o2;
+  ctl.s_e2 = s_e2;
+  ctl.n_o1 = n_o1;
+  ctl.n_o2 = n_o2;
+  ctl.n_i1 = n_i1;
+  ctl.n_d1 = n_d1;
+  ctl.n_i2 = n_i2;
+  ctl.n_d2 = n_d2;
+  ctl.a_i1 = a_i1;
+  ctl.a_i2 = a_i2;
+  ctl.a_d1 = a_d1;
+  ctl.a_d2 = a_d2;
+  const int mns[5] = {sp0.mn, sp1.mn, sp2.mn, sp3.mn, sp4.mn};
+  const int mxs[5] = {sp0.mx, sp1.mx, sp2.mx, sp3.mx, sp4.mx};
+  step_finish(cx, d, ctl, mns, mxs, max_ak, o);
+#ifdef WFA_PROFILE
+  if (cx.tid == 0) {
+    const long long t6 = clock64();
+    unsigned long long* pf = cx.sh->prof;
+    pf[0] += 1;
+    pf[1] += t1 - t0;  // wait at the top barrier
+    pf[2] += t2 - t1;  // metas, limits, row pointers
+    pf[3] += t3 - t2;  // chunk loop (warp 0)
+    pf[4] += t6 - t3;  // step_finish: reduce, second barrier, publish, end test
+    pf[7] += (unsigned long long)(hi - lo + 1);
   }
-  cx.parity ^= 1;
+#endif
   return o;
 }
 
@@ -794,57 +1251,50 @@ WFA_FN int wf_find_breakpoint(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
     return 1;
   }
   rev_max_ak = o.max_ak;
-  bool last_wf_forward = false;
-  while (true) {
-    if (fwd_max_ak + rev_max_ak >= max_antidiagonal) break;
-    ++score_f;
-    o = wf_step(cx, df, pen, score_f);
-    if (o.overflow) return 2;
-    if (fwd_max_ak < o.max_ak) fwd_max_ak = o.max_ak;
-    last_wf_forward = true;
-    if (o.end_reached) {
-      *score_reached = score_f;
-      return 1;
-    }
-    if (fwd_max_ak + rev_max_ak >= max_antidiagonal) break;
-    ++score_r;
-    o = wf_step(cx, dr, pen, score_r);
-    if (o.overflow) return 2;
-    if (rev_max_ak < o.max_ak) rev_max_ak = o.max_ak;
-    last_wf_forward = false;
-    if (o.end_reached) {
-      *score_reached = score_r;
-      return 1;
-    }
-  }
+  // The reference runs two loops (WFA/wavefront_bialign.c:1010-1043 then :1045-1080): first
+  // alternate forward / reverse steps until the wavefronts are close to colliding, then keep
+  // alternating with an overlap search before every step, starting with the direction that did
+  // not move last. Both loops alternate strictly, so they are one loop with a phase flag here
+  // (each step function is instantiated once).
   const int scope = pen.scope;
   const int gap_opening = imax(pen.o1, pen.o2);
+  bool close = false;        // second loop reached
+  bool turn_forward = true;  // direction of the next step
   while (true) {
-    if (last_wf_forward) {
-      const int min_score_r = (score_r > scope - 1) ? score_r - (scope - 1) : 0;
-      cta_sync();
-      if (score_f + min_score_r - gap_opening >= cx.sh->bp.score) break;
-      wf_overlap(cx, df, dr, pen, score_f, score_r, true);
-      ++score_r;
-      o = wf_step(cx, dr, pen, score_r);
+    if (!close && fwd_max_ak + rev_max_ak >= max_antidiagonal) close = true;
+    if (turn_forward) {
+      if (close) {
+        const int min_score_f = (score_f > scope - 1) ? score_f - (scope - 1) : 0;
+        cta_sync();
+        if (min_score_f + score_r - gap_opening >= cx.sh->bp.score) break;
+        wf_overlap(cx, dr, df, pen, score_r, score_f, false);
+      }
+      ++score_f;
+      o = wf_step_vec<false>(cx, df, pen, score_f);
       if (o.overflow) return 2;
+      if (!close && fwd_max_ak < o.max_ak) fwd_max_ak = o.max_ak;
+      if (o.end_reached) {
+        *score_reached = score_f;
+        return 1;
+      }
+      turn_forward = false;
+    } else {
+      if (close) {
+        const int min_score_r = (score_r > scope - 1) ? score_r - (scope - 1) : 0;
+        cta_sync();
+        if (score_f + min_score_r - gap_opening >= cx.sh->bp.score) break;
+        wf_overlap(cx, df, dr, pen, score_f, score_r, true);
+      }
+      ++score_r;
+      o = wf_step_vec<true>(cx, dr, pen, score_r);
+      if (o.overflow) return 2;
+      if (!close && rev_max_ak < o.max_ak) rev_max_ak = o.max_ak;
       if (o.end_reached) {
         *score_reached = score_r;
         return 1;
       }
+      turn_forward = true;
     }
-    const int min_score_f = (score_f > scope - 1) ? score_f - (scope - 1) : 0;
-    cta_sync();
-    if (min_score_f + score_r - gap_opening >= cx.sh->bp.score) break;
-    wf_overlap(cx, dr, df, pen, score_r, score_f, false);
-    ++score_f;
-    o = wf_step(cx, df, pen, score_f);
-    if (o.overflow) return 2;
-    if (o.end_reached) {
-      *score_reached = score_f;
-      return 1;
-    }
-    last_wf_forward = true;
   }
   return 0;
 }
