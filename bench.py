@@ -177,6 +177,10 @@ def main():
     import torch
     import seqrush_b200 as s
 
+    def trace(msg):
+        if os.environ.get("BENCH_TRACE"):
+            print("[bench rank %s] %s" % (os.environ.get("RANK", "0"), msg), file=sys.stderr, flush=True)
+
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -187,6 +191,7 @@ def main():
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        trace("process group up")
 
     ids, seqs, desc = make_workload(args.workload)
     nseq = len(seqs)
@@ -227,8 +232,10 @@ def main():
         torch.cuda.synchronize()
 
     # ---- device-resident timing (value) ----
+    trace("sequences resident, %d pairs on this rank" % my_pairs.shape[0])
     for _ in range(args.warmup):
         step_device()
+        trace("warm-up step done")
         flush.fill_(1)
     barrier()
     sampler = ClockSampler(local)
@@ -246,6 +253,7 @@ def main():
         e1.record(stream)
         barrier()
         step_ms.append(e0.elapsed_time(e1))
+        trace("timed step %d: %.1f ms" % (k, step_ms[-1]))
         for kk in ("align_ms", "union_ms", "wf_cells", "orient_cells", "unite_ops", "unite_links", "aligned_bp",
                    "align_launches", "union_launches"):
             agg[kk] += st[kk]
@@ -275,6 +283,7 @@ def main():
         e1.record(stream)
         barrier()
         e2e_ms.append(e0.elapsed_time(e1))
+        trace("e2e step %d: %.1f ms" % (k, e2e_ms[-1]))
         sr2.union_find.close()
     t = torch.tensor([sum(e2e_ms) / len(e2e_ms)], dtype=torch.float64, device="cuda:%d" % local)
     if dist is not None:

@@ -71,7 +71,7 @@ struct srgpu_ctx {
   std::mutex mu;
   // config
   int threads = 128;
-  int ctas_per_sm = 8;
+  int ctas_per_sm = 4;
   int ring_diagonals = 0;
   // sequences
   uint32_t n_seqs = 0;

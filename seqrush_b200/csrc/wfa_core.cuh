@@ -120,6 +120,7 @@ struct WfStore {
     const int t = cur_slot - (cur_s - s);
     return t < 0 ? t + scope : t;
   }
+  WFA_FN int off_of(int s, int c) const { return (slot(s) * 5 + c) * W + (W >> 1); }  // modular rows only
   WFA_FN int32_t* row_of_slot(int sl, int c) const { return base + (uint32_t)((sl * 5 + c) * W + (W >> 1)); }
   WFA_FN int32_t* row(int s, int c) const {
     if (modular) return row_of_slot(slot(s), c);
@@ -153,6 +154,7 @@ struct CtaShared {
   int ub_r[MAX_SCOPE * 5];
   RedSlots red[2];
   int ovl[MAX_SCOPE * 5];  // overlap search results (min k_0 per task)
+  int wsetup[16][16];      // per warp: row offsets and interior bounds of the running score step
   Frame stack[STACK_MAX];
   int sp;
   Breakpoint bp;
@@ -220,6 +222,21 @@ WFA_FN int ctz32(uint32_t x) {
   return __ffs((int)x) - 1;
 #else
   return __builtin_ctz(x);
+#endif
+}
+// zero-safe variants: 32 for x == 0 (a packed window that matches completely)
+WFA_FN int clz32z(uint32_t x) {
+#if WFA_DEVICE
+  return __clz((int)x);
+#else
+  return x ? __builtin_clz(x) : 32;
+#endif
+}
+WFA_FN int ctz32z(uint32_t x) {
+#if WFA_DEVICE
+  return __clz((int)__brev(x));
+#else
+  return x ? __builtin_ctz(x) : 32;
 #endif
 }
 WFA_FN int clz32(uint32_t x) {
@@ -836,18 +853,6 @@ WFA_FN StepOut wf_step_vec(Ctx& cx, Dir& d, const Penalties& pen, int s) {
     in_lo = imax(in_lo, lo);
     in_hi = imin(in_hi, hi);
   }
-  const int32_t* r_mis = st.row(s_mis < 0 ? 0 : s_mis, C_M);
-  const int32_t* r_o1 = st.row(s_o1 < 0 ? 0 : s_o1, C_M);
-  const int32_t* r_o2 = st.row(s_o2 < 0 ? 0 : s_o2, C_M);
-  const int32_t* r_i1 = st.row(s_e1 < 0 ? 0 : s_e1, C_I1);
-  const int32_t* r_d1 = st.row(s_e1 < 0 ? 0 : s_e1, C_D1);
-  const int32_t* r_i2 = st.row(s_e2 < 0 ? 0 : s_e2, C_I2);
-  const int32_t* r_d2 = st.row(s_e2 < 0 ? 0 : s_e2, C_D2);
-  int32_t* w_m = st.row(s, C_M);
-  int32_t* w_i1 = st.row(s, C_I1);
-  int32_t* w_i2 = st.row(s, C_I2);
-  int32_t* w_d1 = st.row(s, C_D1);
-  int32_t* w_d2 = st.row(s, C_D2);
   const uint32_t tlen = (uint32_t)d.tlen, plen = (uint32_t)d.plen;
   Span4 sp0, sp1, sp2, sp3, sp4;
   sp0.init();
@@ -863,6 +868,36 @@ WFA_FN StepOut wf_step_vec(Ctx& cx, Dir& d, const Penalties& pen, int s) {
   const int warp = 0, nwarps = 1;
 #endif
   constexpr int CH = LANES * 4;
+  // Row offsets (elements from the ring base) and the interior bounds go through a small per-warp
+  // area of shared memory: the chunk loop re-reads them instead of holding 24 pointer registers
+  // (which the compiler otherwise rematerialises from the kernel arguments in every chunk).
+  enum { SU_O1 = 0, SU_O2, SU_I1, SU_I2, SU_D1, SU_D2, SU_MIS, SU_WM, SU_WI1, SU_WI2, SU_WD1, SU_WD2, SU_INLO, SU_INHI };
+  int* su_w = cx.sh->wsetup[warp];
+  if (lane == 0) {
+    su_w[SU_O1] = st.off_of(s_o1 < 0 ? 0 : s_o1, C_M);
+    su_w[SU_O2] = st.off_of(s_o2 < 0 ? 0 : s_o2, C_M);
+    su_w[SU_I1] = st.off_of(s_e1 < 0 ? 0 : s_e1, C_I1);
+    su_w[SU_I2] = st.off_of(s_e2 < 0 ? 0 : s_e2, C_I2);
+    su_w[SU_D1] = st.off_of(s_e1 < 0 ? 0 : s_e1, C_D1);
+    su_w[SU_D2] = st.off_of(s_e2 < 0 ? 0 : s_e2, C_D2);
+    su_w[SU_MIS] = st.off_of(s_mis < 0 ? 0 : s_mis, C_M);
+    su_w[SU_WM] = st.off_of(s, C_M);
+    su_w[SU_WI1] = st.off_of(s, C_I1);
+    su_w[SU_WI2] = st.off_of(s, C_I2);
+    su_w[SU_WD1] = st.off_of(s, C_D1);
+    su_w[SU_WD2] = st.off_of(s, C_D2);
+    su_w[SU_INLO] = in_lo;
+    su_w[SU_INHI] = in_hi;
+  }
+#if WFA_DEVICE
+  __syncwarp();
+#endif
+  const volatile int* su = su_w;
+  int32_t* ring = st.base;
+#if WFA_DEVICE
+  asm volatile("" : "+l"(ring));  // keep the ring base as one materialised 64-bit pointer (row address = one IMAD.WIDE)
+  __builtin_assume(__isGlobal(ring));
+#endif
   PROF_T(t2);
   const int lo_al = lo & ~3;  // arithmetic: rounds towards -inf on two's complement
   for (int kb = lo_al + warp * CH; kb <= hi; kb += nwarps * CH) {
@@ -876,23 +911,29 @@ WFA_FN StepOut wf_step_vec(Ctx& cx, Dir& d, const Penalties& pen, int s) {
     // the row); kq is a safe stand-in address for them
     const bool lane_act = k0 <= hi;
     const int kq = lane_act ? k0 : lo_al;
-    I4 vo1 = ld4(r_o1 + kq), vo2 = ld4(r_o2 + kq), vi1 = ld4(r_i1 + kq), vi2 = ld4(r_i2 + kq);
-    I4 vd1 = ld4(r_d1 + kq), vd2 = ld4(r_d2 + kq), vmis = ld4(r_mis + kq);
+    const int32_t* const r_o1 = ring + (su[SU_O1] + kq);
+    const int32_t* const r_o2 = ring + (su[SU_O2] + kq);
+    const int32_t* const r_i1 = ring + (su[SU_I1] + kq);
+    const int32_t* const r_i2 = ring + (su[SU_I2] + kq);
+    const int32_t* const r_d1 = ring + (su[SU_D1] + kq);
+    const int32_t* const r_d2 = ring + (su[SU_D2] + kq);
+    I4 vo1 = ld4(r_o1), vo2 = ld4(r_o2), vi1 = ld4(r_i1), vi2 = ld4(r_i2);
+    I4 vd1 = ld4(r_d1), vd2 = ld4(r_d2), vmis = ld4(ring + (su[SU_MIS] + kq));
     int32_t o1L = shfl_up1(vo1.w), o2L = shfl_up1(vo2.w), i1L = shfl_up1(vi1.w), i2L = shfl_up1(vi2.w);
     int32_t o1R = shfl_down1(vo1.x), o2R = shfl_down1(vo2.x), d1R = shfl_down1(vd1.x), d2R = shfl_down1(vd2.x);
     if (lane == 0) {
-      o1L = r_o1[kq - 1];
-      o2L = r_o2[kq - 1];
-      i1L = r_i1[kq - 1];
-      i2L = r_i2[kq - 1];
+      o1L = r_o1[-1];
+      o2L = r_o2[-1];
+      i1L = r_i1[-1];
+      i2L = r_i2[-1];
     }
     if (lane == LANES - 1) {
-      o1R = r_o1[kq + 4];
-      o2R = r_o2[kq + 4];
-      d1R = r_d1[kq + 4];
-      d2R = r_d2[kq + 4];
+      o1R = r_o1[4];
+      o2R = r_o2[4];
+      d1R = r_d1[4];
+      d2R = r_d2[4];
     }
-    const bool interior = kb >= in_lo && kb + CH - 1 <= in_hi;  // warp-uniform
+    const bool interior = kb >= su[SU_INLO] && kb + CH - 1 <= su[SU_INHI];  // warp-uniform
     if (!interior) {
       // fringe chunk: whatever lies outside its source wavefront reads as NULL
       // (WFA/wavefront_compute.c:251-295 pads the same way)
@@ -962,10 +1003,10 @@ WFA_FN StepOut wf_step_vec(Ctx& cx, Dir& d, const Penalties& pen, int s) {
     // gap components of this score (rows of components that are not allocated this step are never
     // read: their meta says absent)
     if (lane_act) {
-      st4(w_i1 + k0, ins1[0], ins1[1], ins1[2], ins1[3]);
-      st4(w_i2 + k0, ins2[0], ins2[1], ins2[2], ins2[3]);
-      st4(w_d1 + k0, del1[0], del1[1], del1[2], del1[3]);
-      st4(w_d2 + k0, del2[0], del2[1], del2[2], del2[3]);
+      st4(ring + (su[SU_WI1] + k0), ins1[0], ins1[1], ins1[2], ins1[3]);
+      st4(ring + (su[SU_WI2] + k0), ins2[0], ins2[1], ins2[2], ins2[3]);
+      st4(ring + (su[SU_WD1] + k0), del1[0], del1[1], del1[2], del1[3]);
+      st4(ring + (su[SU_WD2] + k0), del2[0], del2[1], del2[2], del2[3]);
     }
     if (warp_all(all_ok)) {
       // every cell of the chunk is in bounds in all five components (then all are allocated too)
@@ -997,8 +1038,10 @@ WFA_FN StepOut wf_step_vec(Ctx& cx, Dir& d, const Penalties& pen, int s) {
                 a2 && in_bounds(del2[2], k0 + 2, tlen, plen), a3 && in_bounds(del2[3], k0 + 3, tlen, plen), kb);
     }
     PROF_T(tc1);
-    // exact-match extension of the four M cells: the first packed window of all four is compared
-    // together (independent loads overlap); only cells whose whole window matched take the loop
+    // exact-match extension of the four M cells. The first packed window of all four is compared
+    // branch-free (count-zeros returns 32 for a window that matches completely; invalid cells
+    // compare position 0 and are discarded by the select); only cells whose whole window
+    // matched and that have room left walk on through the loop.
     {
       uint32_t xw[4];
       int room[4];
@@ -1006,7 +1049,7 @@ WFA_FN StepOut wf_step_vec(Ctx& cx, Dir& d, const Penalties& pen, int s) {
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const int h = vm[j] ? mx[j] : 0, v = vm[j] ? mx[j] - (k0 + j) : 0;
-        room[j] = vm[j] ? imin(d.plen - v, d.tlen - h) : 0;
+        room[j] = imin(d.plen - v, d.tlen - h);
         if (!REV) {
           xw[j] = pk_window_fwd(d.P, d.p0 + v, d.lbits) ^ pk_window_fwd(d.T, d.t0 + h, d.lbits);
         } else {
@@ -1015,24 +1058,18 @@ WFA_FN StepOut wf_step_vec(Ctx& cx, Dir& d, const Penalties& pen, int s) {
       }
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        if (vm[j]) {
-          int n;
-          if (xw[j]) {
-            n = (REV ? clz32(xw[j]) : ctz32(xw[j])) >> d.lbits;
-          } else {
-            n = per;
-            if (n < room[j]) {
-              const int h = mx[j] + n, v = mx[j] - (k0 + j) + n;
-              n += REV ? lcp_rev(d.P, d.T, d.p0 - v, d.t0 - h, room[j] - n, d.lbits)
-                       : lcp_fwd(d.P, d.T, d.p0 + v, d.t0 + h, room[j] - n, d.lbits);
-            }
-          }
-          mx[j] += imin(n, room[j]);
-          max_ak = imax(max_ak, 2 * mx[j] - (k0 + j));
+        int n = (REV ? clz32z(xw[j]) : ctz32z(xw[j])) >> d.lbits;
+        if (vm[j] && xw[j] == 0 && per < room[j]) {
+          const int h = mx[j] + per, v = mx[j] - (k0 + j) + per;
+          n += REV ? lcp_rev(d.P, d.T, d.p0 - v, d.t0 - h, room[j] - per, d.lbits)
+                   : lcp_fwd(d.P, d.T, d.p0 + v, d.t0 + h, room[j] - per, d.lbits);
         }
+        const int32_t e = mx[j] + imin(n, room[j]);
+        mx[j] = vm[j] ? e : mx[j];
+        max_ak = imax(max_ak, vm[j] ? 2 * e - (k0 + j) : 0);
       }
     }
-    if (lane_act) st4(w_m + k0, mx[0], mx[1], mx[2], mx[3]);
+    if (lane_act) st4(ring + (su[SU_WM] + k0), mx[0], mx[1], mx[2], mx[3]);
 #ifdef WFA_PROFILE
     if (cx.tid == 32 && interior) {
       const long long tc2 = clock64();
@@ -1221,7 +1258,7 @@ WFA_FN void wf_overlap(Ctx& cx, const Dir& d0, const Dir& d1, const Penalties& p
 // ---------------------------------------------------------------------------
 // Breakpoint search (WFA/wavefront_bialign.c:974-1082). Returns:
 //   0 = breakpoint found (in sh->bp), 1 = end reached (score in *score_reached),
-//   2 = workspace overflow.
+//   2 = workspace overflow, 3 = score bound exceeded (reported as unattainable).
 // ---------------------------------------------------------------------------
 WFA_FN int wf_find_breakpoint(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, int* score_reached,
                               unsigned long long* cells) {
@@ -1260,7 +1297,11 @@ WFA_FN int wf_find_breakpoint(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
   const int gap_opening = imax(pen.o1, pen.o2);
   bool close = false;        // second loop reached
   bool turn_forward = true;  // direction of the next step
+  // no alignment costs more than deleting the pattern and inserting the text; a search that runs
+  // past that bound is broken (workspace corruption) and is reported instead of spinning forever
+  const long long score_bound = 2ll * imax(pen.o1, pen.o2) + (long long)(df.plen + df.tlen) * imax(pen.e1, pen.e2) + 64;
   while (true) {
+    if ((long long)score_f + score_r > score_bound) return 3;
     if (!close && fwd_max_ak + rev_max_ak >= max_antidiagonal) close = true;
     if (turn_forward) {
       if (close) {
@@ -1599,6 +1640,10 @@ WFA_FN PairResult wf_align_pair(Ctx& cx, const SeqView& sv, int plen, int tlen, 
     const int r = wf_find_breakpoint(cx, df, dr, pen, &score_reached, nullptr);
     if (r == 2) {
       if (cx.tid == 0) sh->status = ST_WS_DIAG_OVERFLOW;
+      continue;
+    }
+    if (r == 3) {
+      if (cx.tid == 0) sh->status = ST_UNATTAINABLE;
       continue;
     }
     if (r == 1) {

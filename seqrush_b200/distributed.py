@@ -27,10 +27,20 @@ def merge_forests(local_roots, world: int, dist, unite_with_peer):
 
 def merge_device_union_finds(uf, dist):
     """NCCL path: uf is a seqrush_b200.BidirectedUnionFind."""
+    import torch
+
     uf.compress()
     t = uf.as_tensor()
     world = dist.get_world_size()
     if world == 1:
         return
-    merge_forests(t, world, dist, lambda peer: uf.merge_roots(peer.data_ptr(), peer.numel()))
+    # the library launches on the context's own stream, NCCL on torch's: order them explicitly
+    # (compress -> all_gather -> merge), once per step
+    uf.ctx.synchronize()
+
+    def unite_with_peer(peer):
+        torch.cuda.current_stream(peer.device).synchronize()
+        uf.merge_roots(peer.data_ptr(), peer.numel())
+
+    merge_forests(t, world, dist, unite_with_peer)
     uf.compress()
