@@ -221,9 +221,12 @@ def main():
 
     def step_device():
         reset_uf()
+        trace("union-find reset")
         st = sr.align_and_unite_device(d_pairs.data_ptr(), my_pairs.shape[0], sargs)
+        trace("align+unite done: %.0f ms align, %d launches, %d retries" % (st["align_ms"], st["kernel_launches"], st["retries"]))
         if dist is not None:
             merge_device_union_finds(sr.union_find, dist)
+            trace("forests merged")
         return st
 
     def barrier():

@@ -443,13 +443,15 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
   if ((rc = c->d_runs_tmp.ensure((size_t)grid * runs_cap))) return rc;
   if ((rc = c->d_bt_tmp.ensure((size_t)grid * runs_cap))) return rc;
   // arena: run-length CIGAR elements of one chunk
-  size_t arena_cap = std::max<size_t>((size_t)64 << 20, 4 * runs_cap);  // 64M runs = 256 MB
+  size_t arena_cap = std::max<size_t>((size_t)256 << 20, 4 * runs_cap);  // 256M runs = 1 GB
   if (keep_runs) arena_cap = std::max<size_t>(arena_cap, std::min<size_t>((size_t)n_pairs * runs_cap, (size_t)1 << 30));
   if ((rc = c->d_arena.ensure(arena_cap))) return rc;
-  // chunking: assume <= 1 run per 4 columns on average; overflow is detected and retried
-  uint64_t chunk = keep_runs ? n_pairs : std::max<uint64_t>(1, arena_cap / std::max<size_t>(1, runs_cap / 4));
+  // chunking: assume <= 1 run per 16 columns on average (3% divergence); overflow is detected and the
+  // pairs that did not fit are re-run. Few large launches keep the end-of-launch tail (CTAs idling while
+  // the last pairs finish) small against the launch.
+  uint64_t chunk = keep_runs ? n_pairs : std::max<uint64_t>(1, arena_cap / std::max<size_t>(1, runs_cap / 16));
   chunk = std::min<uint64_t>(chunk, n_pairs);
-  if (!keep_runs) chunk = std::min<uint64_t>(chunk, std::max<uint64_t>((uint64_t)grid * 8, 4096));
+  if (!keep_runs) chunk = std::min<uint64_t>(chunk, std::max<uint64_t>((uint64_t)grid * 64, 4096));
 
   AlignArgs a;
   a.seqs = seq_table(c);

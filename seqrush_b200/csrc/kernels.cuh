@@ -122,7 +122,13 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   uint32_t done = 0;
+  const long long t_start = clock64();
   while (!done) {
+    // a bulk copy that never lands would spin here forever: fail loudly instead (about 5 s)
+    if (clock64() - t_start > 10000000000ll) {
+      printf("seqrush_b200: bulk copy of a sequence pair did not complete (CTA %d)\n", (int)blockIdx.x);
+      __trap();
+    }
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
@@ -213,7 +219,9 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
     sv.p = orr.is_reverse ? Pr : Pf;
     sv.t = T;
     sv.lbits = lbits;
-    const PairResult r = wf_align_pair(cx, sv, (int)plen, (int)tlen, a.pen, ws, ro);
+    // an alignment with `distance` unit edits costs at most max(x, cheapest one-base gap) per edit
+    const long long per_edit = max(a.pen.x, min(a.pen.o1 + a.pen.e1, a.pen.o2 + a.pen.e2));
+    const PairResult r = wf_align_pair(cx, sv, (int)plen, (int)tlen, a.pen, ws, ro, per_edit * (long long)orr.distance);
     // 3. finalize: CIGAR statistics (allwave/src/alignment.rs:279-324), penalty
     //    (WFA2-lib/alignment/cigar.c:303-343), copy the runs into the chunk arena
     __syncthreads();

@@ -1261,8 +1261,7 @@ WFA_FN void wf_overlap(Ctx& cx, const Dir& d0, const Dir& d1, const Penalties& p
 //   2 = workspace overflow, 3 = score bound exceeded (reported as unattainable).
 // ---------------------------------------------------------------------------
 WFA_FN int wf_find_breakpoint(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, int* score_reached,
-                              unsigned long long* cells) {
-  (void)cells;
+                              long long score_hint) {
   cta_sync();
   df.st.cur_s = INT32_MIN / 2;
   dr.st.cur_s = INT32_MIN / 2;
@@ -1297,9 +1296,14 @@ WFA_FN int wf_find_breakpoint(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
   const int gap_opening = imax(pen.o1, pen.o2);
   bool close = false;        // second loop reached
   bool turn_forward = true;  // direction of the next step
-  // no alignment costs more than deleting the pattern and inserting the text; a search that runs
-  // past that bound is broken (workspace corruption) and is reported instead of spinning forever
-  const long long score_bound = 2ll * imax(pen.o1, pen.o2) + (long long)(df.plen + df.tlen) * imax(pen.e1, pen.e2) + 64;
+  // The two searches meet once score_f + score_r passes the optimal penalty by at most a few
+  // scopes. score_hint bounds that penalty from above (sub-problems: the exact score the parent's
+  // breakpoint assigned; level 0: what the edit-distance alignment of the strand choice would cost;
+  // else deleting the pattern and inserting the text). A search that runs past the bound is broken
+  // (workspace corruption) and is reported as unattainable instead of spinning on.
+  long long score_bound = 2ll * imax(pen.o1, pen.o2) + (long long)(df.plen + df.tlen) * imax(pen.e1, pen.e2);
+  if (score_hint < score_bound) score_bound = score_hint;
+  score_bound += 4ll * pen.scope + 64;
   while (true) {
     if ((long long)score_f + score_r > score_bound) return 3;
     if (!close && fwd_max_ak + rev_max_ak >= max_antidiagonal) close = true;
@@ -1566,7 +1570,7 @@ WFA_FN void set_dirs(Dir& df, Dir& dr, Dir& db, const SeqView& sv, const Frame& 
 }
 
 WFA_FN PairResult wf_align_pair(Ctx& cx, const SeqView& sv, int plen, int tlen, const Penalties& pen,
-                                const PairWorkspace& ws, const RunOut& ro) {
+                                const PairWorkspace& ws, const RunOut& ro, long long score_hint = INT64_MAX) {
   CtaShared* sh = cx.sh;
   PairResult res;
   res.status = ST_OK;
@@ -1637,7 +1641,8 @@ WFA_FN PairResult wf_align_pair(Ctx& cx, const SeqView& sv, int plen, int tlen, 
       continue;
     }
     int score_reached = 0;
-    const int r = wf_find_breakpoint(cx, df, dr, pen, &score_reached, nullptr);
+    const int r = wf_find_breakpoint(cx, df, dr, pen, &score_reached,
+                                     f.level == 0 ? score_hint : (long long)f.score_remaining);
     if (r == 2) {
       if (cx.tid == 0) sh->status = ST_WS_DIAG_OVERFLOW;
       continue;
