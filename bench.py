@@ -54,7 +54,7 @@ class ClockSampler:
              "clocks_event_reasons.sw_power_cap")
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q,
-                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                          "--format=csv,noheader,nounits", "-lms", "1000"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -217,8 +217,7 @@ def main():
     sargs = s.Args(min_match_length=0)
 
     def reset_uf():
-        sr.union_find.close()
-        sr.union_find = s.BidirectedUnionFind(total_len, ctx)
+        sr.union_find.clear()  # UFRush::clear, then SeqRush::new's unite(2i, 2i+1) loop (src/seqrush.rs:324-328)
         sr.union_find.unite_fr_all(total_len)
 
     def step_device():

@@ -139,6 +139,7 @@ int srgpu_process_alignment(srgpu_ctx* ctx, srgpu_uf* uf, const char* cigar, uin
 int srgpu_uf_new(srgpu_ctx* ctx, uint64_t max_offset, srgpu_uf** out); /* ::new, :16-24: capacity 2*max_offset+2 */
 void srgpu_uf_free(srgpu_uf* uf);
 uint64_t srgpu_uf_capacity(srgpu_uf* uf);
+int srgpu_uf_clear(srgpu_uf* uf); /* UFRush::clear, uf_rush-0.2.1/src/lib.rs:211-216: all singletons again */
 int srgpu_uf_find(srgpu_uf* uf, uint64_t pos, uint64_t* rep);             /* ::find, :27-31 */
 int srgpu_uf_same(srgpu_uf* uf, uint64_t a, uint64_t b, int* same);       /* ::same, :46-54 */
 int srgpu_uf_unite(srgpu_uf* uf, uint64_t a, uint64_t b);                 /* ::unite, :35-43 */

@@ -20,7 +20,7 @@ EXPORTS = [
     "srgpu_last_error", "srgpu_ctx_create", "srgpu_ctx_destroy", "srgpu_ctx_synchronize", "srgpu_ctx_configure",
     "srgpu_ctx_stats", "srgpu_set_sequences", "srgpu_total_length", "srgpu_align_pairs", "srgpu_free",
     "srgpu_align_and_unite", "srgpu_align_and_unite_device", "srgpu_process_alignment", "srgpu_uf_new",
-    "srgpu_uf_free", "srgpu_uf_capacity", "srgpu_uf_find", "srgpu_uf_same", "srgpu_uf_unite",
+    "srgpu_uf_free", "srgpu_uf_capacity", "srgpu_uf_clear", "srgpu_uf_find", "srgpu_uf_same", "srgpu_uf_unite",
     "srgpu_uf_unite_matching_region", "srgpu_uf_unite_matching_region_seq2_rc", "srgpu_uf_unite_regions",
     "srgpu_uf_unite_fr_all", "srgpu_uf_roots", "srgpu_uf_count_components", "srgpu_uf_checksum",
     "srgpu_uf_device_ptr", "srgpu_uf_compress", "srgpu_uf_merge_roots",
@@ -117,6 +117,7 @@ def lib():
     L.srgpu_uf_free.restype = None
     L.srgpu_uf_capacity.argtypes = [vp]
     L.srgpu_uf_capacity.restype = u64
+    L.srgpu_uf_clear.argtypes = [vp]
     L.srgpu_uf_find.argtypes = [vp, u64, C.POINTER(u64)]
     L.srgpu_uf_same.argtypes = [vp, u64, u64, C.POINTER(i32)]
     L.srgpu_uf_unite.argtypes = [vp, u64, u64]

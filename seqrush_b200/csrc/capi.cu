@@ -777,6 +777,20 @@ extern "C" void srgpu_uf_free(srgpu_uf* u) {
 
 extern "C" uint64_t srgpu_uf_capacity(srgpu_uf* u) { return u ? u->capacity : 0; }
 
+// UFRush::clear (uf_rush-0.2.1/src/lib.rs:211-216): every Pos back to its own singleton set
+extern "C" int srgpu_uf_clear(srgpu_uf* u) {
+  if (!u) return SRGPU_E_ARG;
+  UF_ALIVE(u);
+  srgpu_ctx* c = u->ctx;
+  std::lock_guard<std::mutex> lk(c->mu);
+  CK(cudaSetDevice(c->device));
+  uf_init_kernel<<<grid_for(u->capacity, 256, c->n_sm), 256, 0, c->stream>>>(u->parent.p, u->capacity);
+  CK(cudaGetLastError());
+  CK(cudaMemsetAsync(u->counters.p, 0, 8 * sizeof(unsigned long long), c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  return SRGPU_OK;
+}
+
 extern "C" int srgpu_uf_roots(srgpu_uf* u, uint64_t first, uint64_t n, uint64_t* out) {
   if (!u || (!out && n)) return SRGPU_E_ARG;
   UF_ALIVE(u);

@@ -33,7 +33,11 @@ __device__ __forceinline__ uint32_t uf_find(uint32_t* __restrict__ parent, uint3
 // returns true when two roots were linked
 __device__ __forceinline__ bool uf_unite(uint32_t* __restrict__ parent, uint32_t a, uint32_t b) {
   if (a == b) return false;  // src/bidirected_union_find.rs:40
-  uint32_t ra = uf_find(parent, a), rb = uf_find(parent, b);
+  // most unite calls of an all-vs-all run are redundant (the two Pos already share a set, usually
+  // as children of the same root after path halving): two reads settle those
+  const uint32_t pa = parent[a], pb = parent[b];
+  if (pa == pb || pa == b || pb == a) return false;
+  uint32_t ra = uf_find(parent, pa), rb = uf_find(parent, pb);
   while (ra != rb) {
     if (ra < rb) {
       const uint32_t t = ra;
@@ -546,13 +550,11 @@ __global__ void __launch_bounds__(THREADS) union_kernel(UnionArgs a) {
       __syncthreads();
       // flattened loop over the united bases of this tile: consecutive threads take consecutive
       // bases, so the parent[] reads of a warp fall into one or two 128-byte lines per side
+      // run index of base u = largest i with s_cum[i] <= u; u grows by THREADS per iteration, so the
+      // index only moves forward: a short linear advance replaces a binary search per base
+      uint32_t lo = 0;
       for (uint32_t u = threadIdx.x; u < tile_total; u += THREADS) {
-        // largest i with s_cum[i] <= u (upper_bound - 1)
-        uint32_t lo = 0, hi = UNION_TILE;
-        while (hi - lo > 1) {
-          const uint32_t mid = (lo + hi) >> 1;
-          if (s_cum[mid] <= u) lo = mid; else hi = mid;
-        }
+        while (s_cum[lo + 1] <= u) ++lo;
         const uint32_t within = u - s_cum[lo];
         const uint32_t p1 = s_qpos[lo] + within, p2 = s_tpos[lo] + within;
         uint32_t x, y;

@@ -287,6 +287,37 @@ WFA_FN int lcp_rev(const uint32_t* P, const uint32_t* T, int v, int h, int maxle
   return n < maxlen ? n : maxlen;
 }
 
+// Direction-agnostic forms (rev = 0/1 at run time): one copy of the score-step code serves both
+// aligners of a breakpoint search, which halves the hot instruction footprint per SM.
+//   rev = 0: 32 bits of packed symbols starting at symbol i (low bits first)
+//   rev = 1: 32 bits ending with symbol i in the top bits
+WFA_FN uint32_t pk_window_dir(const uint32_t* a, int i, int lbits, int rev) {
+  const uint32_t bit = (uint32_t)(i + rev) << lbits;
+  const uint32_t* w = a + (bit >> 5) - rev;
+  return funnel_r(w[0], w[1], bit);
+}
+// matching symbols at the near end of an XORed window pair (32 >> lbits when it is all zero)
+WFA_FN int pk_match_len(uint32_t x, int lbits, int rev) {
+#if WFA_DEVICE
+  return __clz((int)(rev ? x : __brev(x))) >> lbits;
+#else
+  return (rev ? clz32z(x) : ctz32z(x)) >> lbits;
+#endif
+}
+WFA_FN int lcp_dir(const uint32_t* P, const uint32_t* T, int v, int h, int maxlen, int lbits, int rev) {
+  int n = 0;
+  const int per = 32 >> lbits, sgn = rev ? -1 : 1;
+  while (n < maxlen) {
+    const uint32_t x = pk_window_dir(P, v + sgn * n, lbits, rev) ^ pk_window_dir(T, h + sgn * n, lbits, rev);
+    if (x) {
+      n += pk_match_len(x, lbits, rev);
+      break;
+    }
+    n += per;
+  }
+  return n < maxlen ? n : maxlen;
+}
+
 // One aligner direction over the current sub-problem.
 struct Dir {
   WfStore st;
@@ -350,8 +381,8 @@ WFA_FN bool wf_end_reached(const Dir& d, int score) {
 WFA_FN int wf_extend_cell(const Dir& d, int k, int32_t off) {
   const int v = off - k, h = off;
   const int room = imin(d.plen - v, d.tlen - h);
-  if (!d.reverse) return off + lcp_fwd(d.P, d.T, d.p0 + v, d.t0 + h, room, d.lbits);
-  return off + lcp_rev(d.P, d.T, d.p0 - v, d.t0 - h, room, d.lbits);
+  const int sgn = d.reverse ? -1 : 1;
+  return off + lcp_dir(d.P, d.T, d.p0 + sgn * v, d.t0 + sgn * h, room, d.lbits, d.reverse);
 }
 
 // score-0 extension: a single cell at most (k=0), done by thread 0. Every thread runs set_cur so
@@ -787,15 +818,6 @@ struct Span4 {
   }
 };
 
-template <bool REV>
-WFA_FN int wf_extend_cell_t(const Dir& d, int k, int32_t off) {
-  const int v = off - k, h = off;
-  const int room = imin(d.plen - v, d.tlen - h);
-  if (!REV) return off + lcp_fwd(d.P, d.T, d.p0 + v, d.t0 + h, room, d.lbits);
-  return off + lcp_rev(d.P, d.T, d.p0 - v, d.t0 - h, room, d.lbits);
-}
-
-template <bool REV>
 WFA_FN StepOut wf_step_vec(Ctx& cx, Dir& d, const Penalties& pen, int s) {
   StepOut o;
   o.null_step = 0;
@@ -1046,23 +1068,19 @@ WFA_FN StepOut wf_step_vec(Ctx& cx, Dir& d, const Penalties& pen, int s) {
       uint32_t xw[4];
       int room[4];
       const int per = 32 >> d.lbits;
+      const int rev = d.reverse, sgn = rev ? -1 : 1;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const int h = vm[j] ? mx[j] : 0, v = vm[j] ? mx[j] - (k0 + j) : 0;
         room[j] = imin(d.plen - v, d.tlen - h);
-        if (!REV) {
-          xw[j] = pk_window_fwd(d.P, d.p0 + v, d.lbits) ^ pk_window_fwd(d.T, d.t0 + h, d.lbits);
-        } else {
-          xw[j] = pk_window_rev(d.P, d.p0 - v, d.lbits) ^ pk_window_rev(d.T, d.t0 - h, d.lbits);
-        }
+        xw[j] = pk_window_dir(d.P, d.p0 + sgn * v, d.lbits, rev) ^ pk_window_dir(d.T, d.t0 + sgn * h, d.lbits, rev);
       }
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        int n = (REV ? clz32z(xw[j]) : ctz32z(xw[j])) >> d.lbits;
+        int n = pk_match_len(xw[j], d.lbits, rev);
         if (vm[j] && xw[j] == 0 && per < room[j]) {
           const int h = mx[j] + per, v = mx[j] - (k0 + j) + per;
-          n += REV ? lcp_rev(d.P, d.T, d.p0 - v, d.t0 - h, room[j] - per, d.lbits)
-                   : lcp_fwd(d.P, d.T, d.p0 + v, d.t0 + h, room[j] - per, d.lbits);
+          n += lcp_dir(d.P, d.T, d.p0 + sgn * v, d.t0 + sgn * h, room[j] - per, d.lbits, rev);
         }
         const int32_t e = mx[j] + imin(n, room[j]);
         mx[j] = vm[j] ? e : mx[j];
@@ -1307,39 +1325,41 @@ WFA_FN int wf_find_breakpoint(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
   while (true) {
     if ((long long)score_f + score_r > score_bound) return 3;
     if (!close && fwd_max_ak + rev_max_ak >= max_antidiagonal) close = true;
-    if (turn_forward) {
-      if (close) {
-        const int min_score_f = (score_f > scope - 1) ? score_f - (scope - 1) : 0;
-        cta_sync();
-        if (min_score_f + score_r - gap_opening >= cx.sh->bp.score) break;
-        wf_overlap(cx, dr, df, pen, score_r, score_f, false);
-      }
-      ++score_f;
-      o = wf_step_vec<false>(cx, df, pen, score_f);
-      if (o.overflow) return 2;
-      if (!close && fwd_max_ak < o.max_ak) fwd_max_ak = o.max_ak;
-      if (o.end_reached) {
-        *score_reached = score_f;
-        return 1;
-      }
-      turn_forward = false;
-    } else {
-      if (close) {
-        const int min_score_r = (score_r > scope - 1) ? score_r - (scope - 1) : 0;
-        cta_sync();
-        if (score_f + min_score_r - gap_opening >= cx.sh->bp.score) break;
-        wf_overlap(cx, df, dr, pen, score_f, score_r, true);
-      }
-      ++score_r;
-      o = wf_step_vec<true>(cx, dr, pen, score_r);
-      if (o.overflow) return 2;
-      if (!close && rev_max_ak < o.max_ak) rev_max_ak = o.max_ak;
-      if (o.end_reached) {
-        *score_reached = score_r;
-        return 1;
-      }
-      turn_forward = true;
+    const bool tf = turn_forward;
+    const int own = tf ? score_f : score_r, oth = tf ? score_r : score_f;
+    if (close) {
+      const int min_own = (own > scope - 1) ? own - (scope - 1) : 0;
+      cta_sync();
+      if (min_own + oth - gap_opening >= cx.sh->bp.score) break;
+      // the wavefront that moved last is searched against the scope of the one about to move
+      const Dir a = tf ? dr : df, b = tf ? df : dr;
+      wf_overlap(cx, a, b, pen, oth, own, !tf);
     }
+    // one copy of the step code for both directions: the moving aligner is selected into d
+    Dir d = tf ? df : dr;
+    o = wf_step_vec(cx, d, pen, own + 1);
+    if (tf) {
+      df.st.cur_s = d.st.cur_s;
+      df.st.cur_slot = d.st.cur_slot;
+      ++score_f;
+    } else {
+      dr.st.cur_s = d.st.cur_s;
+      dr.st.cur_slot = d.st.cur_slot;
+      ++score_r;
+    }
+    if (o.overflow) return 2;
+    if (!close) {
+      if (tf) {
+        if (fwd_max_ak < o.max_ak) fwd_max_ak = o.max_ak;
+      } else {
+        if (rev_max_ak < o.max_ak) rev_max_ak = o.max_ak;
+      }
+    }
+    if (o.end_reached) {
+      *score_reached = own + 1;
+      return 1;
+    }
+    turn_forward = !tf;
   }
   return 0;
 }

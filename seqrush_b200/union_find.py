@@ -21,6 +21,9 @@ class BidirectedUnionFind:
     def new(cls, max_offset: int, ctx=None):
         return cls(max_offset, ctx)
 
+    def clear(self):  # UFRush::clear (uf_rush lib.rs:211-216)
+        _lib.check(_lib.lib().srgpu_uf_clear(self._h))
+
     def close(self):
         if getattr(self, "_h", None) and self._h.value:
             _lib.lib().srgpu_uf_free(self._h)
