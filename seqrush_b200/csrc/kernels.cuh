@@ -208,7 +208,13 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
       T = s_seq + 2 * a.smem_seq_words + 4;
     }
     // 1. strand (allwave/src/alignment.rs:24-30)
+#ifdef WFA_PROFILE
+    const long long t_or0 = clock64();
+#endif
     const OrientResult orr = wf_orient(cx, Pf, Pr, T, lbits, (int)plen, (int)tlen, obuf, a.orient_row);
+#ifdef WFA_PROFILE
+    const long long t_or1 = clock64();
+#endif
     // 2. BiWFA (allwave/src/alignment.rs:189-276). Ring rows are sized from the edit distance just
     //    found (penalty <= 10 per edit, about half of it per direction); a pair that still
     //    overflows is reported and re-run by the host with full-width rows.
@@ -226,6 +232,13 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
     // an alignment with `distance` unit edits costs at most max(x, cheapest one-base gap) per edit
     const long long per_edit = max(a.pen.x, min(a.pen.o1 + a.pen.e1, a.pen.o2 + a.pen.e2));
     const PairResult r = wf_align_pair(cx, sv, (int)plen, (int)tlen, a.pen, ws, ro, per_edit * (long long)orr.distance);
+#ifdef WFA_PROFILE
+    if (threadIdx.x == 0) {
+      sh.prof[13] += t_or1 - t_or0;         // strand choice
+      sh.prof[14] += clock64() - t_or1;     // BiWFA
+      sh.prof[15] += (unsigned long long)orr.distance;
+    }
+#endif
     // 3. finalize: CIGAR statistics (allwave/src/alignment.rs:279-324), penalty
     //    (WFA2-lib/alignment/cigar.c:303-343), copy the runs into the chunk arena
     __syncthreads();
@@ -302,6 +315,7 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
     printf("[prof cta %d] ring steps %llu  total cyc %lld | per step: top-barrier %.0f  setup %.0f  loop %.0f  finish %.0f  "
            "| avg width %.0f\n",
            (int)blockIdx.x, pf[0], clock64() - prof_start, pf[1] / n, pf[2] / n, pf[3] / n, pf[4] / n, pf[7] / n);
+    printf("[prof cta %d] strand choice %llu cyc (sum of edit distances %llu), BiWFA %llu cyc\n", (int)blockIdx.x, pf[13], pf[15], pf[14]);
     printf("[prof cta %d] warp1 interior chunks %llu: compute %.0f cyc, extend %.0f cyc | warp0 fringe chunks %llu: %.0f cyc\n",
            (int)blockIdx.x, pf[8], pf[9] / (pf[8] ? (double)pf[8] : 1.0), pf[10] / (pf[8] ? (double)pf[8] : 1.0), pf[11],
            pf[12] / (pf[11] ? (double)pf[11] : 1.0));

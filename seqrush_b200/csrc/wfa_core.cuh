@@ -155,6 +155,7 @@ struct CtaShared {
   RedSlots red[2];
   int ovl[MAX_SCOPE * 5];  // overlap search results (min k_0 per task)
   int wsetup[16][16];      // per warp: row offsets and interior bounds of the running score step
+  int chunk_ctr;           // next unclaimed chunk of the running score step (dynamic balance)
   Frame stack[STACK_MAX];
   int sp;
   Breakpoint bp;
@@ -525,8 +526,11 @@ WFA_FN void step_finish(Ctx& cx, const Dir& d, const StepCtl& t, const int* mn, 
     int* nx = &cx.sh->red[cx.parity ^ 1].mn[0];
     const int i = cx.tid - 5;
     nx[i] = i < 5 ? INT32_MAX : i < 10 ? INT32_MIN : 0;
+  } else if (cx.tid == 16) {
+    cx.sh->chunk_ctr = 0;  // every warp is past its last claim (barrier above)
   }
 #else
+  cx.sh->chunk_ctr = 0;
   for (int c = 0; c < 5; ++c) publish_comp(st, red, t, c);
   {
     RedSlots* nx = &cx.sh->red[cx.parity ^ 1];
@@ -922,7 +926,22 @@ WFA_FN StepOut wf_step_vec(Ctx& cx, Dir& d, const Penalties& pen, int s) {
 #endif
   PROF_T(t2);
   const int lo_al = lo & ~3;  // arithmetic: rounds towards -inf on two's complement
-  for (int kb = lo_al + warp * CH; kb <= hi; kb += nwarps * CH) {
+  // Chunks are claimed from a shared counter instead of being dealt round-robin: the two fringe
+  // chunks (masked reads, per-cell trims: ~1.5x an interior chunk) go first, then the interior, so
+  // the warps reach the closing barrier of the step together whatever the chunks cost.
+  const int nchunks = (hi - lo_al) / CH + 1;
+  (void)nwarps;
+  while (true) {
+    int claim = 0;
+#if WFA_DEVICE
+    if (lane == 0) claim = atomicAdd(&cx.sh->chunk_ctr, 1);
+    claim = __shfl_sync(0xffffffffu, claim, 0);
+#else
+    claim = cx.sh->chunk_ctr++;
+#endif
+    if (claim >= nchunks) break;
+    const int ci = claim == 0 ? 0 : (claim == 1 ? nchunks - 1 : claim - 1);
+    const int kb = lo_al + ci * CH;
     const int k0 = kb + 4 * lane;
     int32_t ins1[4], ins2[4], del1[4], del2[4], mx[4];
     bool vm[4];
@@ -1148,6 +1167,7 @@ WFA_FN void red_reset(Ctx& cx) {
       }
       cx.sh->red[b].max_ak = 0;
     }
+    cx.sh->chunk_ctr = 0;
   }
   cx.parity = 0;
 }
