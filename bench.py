@@ -314,6 +314,10 @@ def main():
     r0_cells, r0_ocells = agg["wf_cells"], agg["orient_cells"]
     n_launch = max(1, agg["align_launches"])
     BYTES_PER_CELL = 48  # 7 source offsets read + 5 offsets written, int32 (DESIGN.md "roofline")
+    # measured DRAM traffic of the align kernel per wavefront cell: dram__bytes_read.sum + dram__bytes_write.sum
+    # = 856.0 GB over the 2.052e10 cells of a 600-pair c2 launch (ncu --set full, profiles/r01g_ncu_align_kernel_c2.txt);
+    # scaled by this launch's cell count because the full launch is too long to replay under ncu
+    DRAM_BYTES_PER_CELL_NCU = 856.0e9 / 2.052e10
     alg_bytes = BYTES_PER_CELL * r0_cells + 16 * r0_ocells
     INT_OPS_PER_CELL = 17 + 6  # 17 int ops per cell + 6 per extend word (>= 1 word per cell)
     int_peak = 148 * 4 * 32 * sm_max_mhz * 1e6
@@ -334,7 +338,10 @@ def main():
         "clocks": clocks,
         "roofline": {"kernel": "align_kernel (orientation + BiWFA + backtrace)", "bound": "hbm",
                      "achieved": alg_bytes / al_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": alg_bytes / al_s / 1e9 / hbm_peak, "traffic": None, "peak_kind": peak_kind,
+                     "frac": alg_bytes / al_s / 1e9 / hbm_peak,
+                     "traffic": DRAM_BYTES_PER_CELL_NCU * r0_cells / n_launch if args.workload == "c2" else None,
+                     "traffic_unit": "bytes per launch (ncu-measured bytes per cell x cells of this launch)",
+                     "peak_kind": peak_kind,
                      "algorithmic_bytes_per_launch": alg_bytes / n_launch, "avg_launch_ms": agg["align_ms"] / n_launch,
                      "share_of_step": agg["align_ms"] / sum(step_ms)},
         "roofline_int_issue": {"kernel": "align_kernel", "bound": "int_issue",

@@ -31,12 +31,12 @@ __device__ __forceinline__ uint32_t uf_find(uint32_t* __restrict__ parent, uint3
   return x;
 }
 // returns true when two roots were linked
-__device__ __forceinline__ bool uf_unite(uint32_t* __restrict__ parent, uint32_t a, uint32_t b) {
-  if (a == b) return false;  // src/bidirected_union_find.rs:40
+// second half of a unite whose two parent reads (pa = parent[a], pb = parent[b]) are already there
+__device__ __forceinline__ bool uf_unite_from(uint32_t* __restrict__ parent, uint32_t a, uint32_t b, uint32_t pa,
+                                              uint32_t pb) {
   // most unite calls of an all-vs-all run are redundant (the two Pos already share a set, usually
-  // as children of the same root after path halving): two reads settle those
-  const uint32_t pa = parent[a], pb = parent[b];
-  if (pa == pb || pa == b || pb == a) return false;
+  // as children of the same root after path halving): the two reads settle those
+  if (a == b || pa == pb || pa == b || pb == a) return false;  // a == b: src/bidirected_union_find.rs:40
   uint32_t ra = uf_find(parent, pa), rb = uf_find(parent, pb);
   while (ra != rb) {
     if (ra < rb) {
@@ -50,6 +50,10 @@ __device__ __forceinline__ bool uf_unite(uint32_t* __restrict__ parent, uint32_t
     rb = uf_find(parent, rb);
   }
   return false;
+}
+__device__ __forceinline__ bool uf_unite(uint32_t* __restrict__ parent, uint32_t a, uint32_t b) {
+  if (a == b) return false;
+  return uf_unite_from(parent, a, b, parent[a], parent[b]);
 }
 
 // ---------------------------------------------------------------------------
@@ -566,20 +570,30 @@ __global__ void __launch_bounds__(THREADS) union_kernel(UnionArgs a) {
       // bases, so the parent[] reads of a warp fall into one or two 128-byte lines per side
       // run index of base u = largest i with s_cum[i] <= u; u grows by THREADS per iteration, so the
       // index only moves forward: a short linear advance replaces a binary search per base
+      // Four bases per thread and iteration: their eight parent reads are issued together (the
+      // kernel is bound by the latency of these scattered 4-byte reads, not by bandwidth).
       uint32_t lo = 0;
-      for (uint32_t u = threadIdx.x; u < tile_total; u += THREADS) {
-        while (s_cum[lo + 1] <= u) ++lo;
-        const uint32_t within = u - s_cum[lo];
-        const uint32_t p1 = s_qpos[lo] + within, p2 = s_tpos[lo] + within;
-        uint32_t x, y;
-        if (rc) {
-          x = (uint32_t)(2 * (qoff + qlen - 1 - p1) + 1);
-        } else {
-          x = (uint32_t)(2 * (qoff + p1));
+      constexpr int UNR = 4;
+      for (uint32_t u0 = threadIdx.x; u0 < tile_total; u0 += UNR * THREADS) {
+        uint32_t x[UNR], y[UNR], px[UNR], py[UNR];
+#pragma unroll
+        for (int j = 0; j < UNR; ++j) {
+          const uint32_t u = u0 + j * THREADS;
+          x[j] = y[j] = 0;
+          if (u < tile_total) {
+            while (s_cum[lo + 1] <= u) ++lo;
+            const uint32_t within = u - s_cum[lo];
+            const uint32_t p1 = s_qpos[lo] + within, p2 = s_tpos[lo] + within;
+            x[j] = rc ? (uint32_t)(2 * (qoff + qlen - 1 - p1) + 1) : (uint32_t)(2 * (qoff + p1));
+            y[j] = (uint32_t)(2 * (toff + p2));
+            ++ops;
+          }
+          px[j] = a.parent[x[j]];
+          py[j] = a.parent[y[j]];
         }
-        y = (uint32_t)(2 * (toff + p2));
-        ++ops;
-        if (uf_unite(a.parent, x, y)) ++links;
+#pragma unroll
+        for (int j = 0; j < UNR; ++j)
+          if (uf_unite_from(a.parent, x[j], y[j], px[j], py[j])) ++links;
       }
       __syncthreads();
       if (threadIdx.x == 0) {
