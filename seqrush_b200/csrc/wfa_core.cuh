@@ -960,19 +960,34 @@ WFA_FN StepOut wf_step_vec(Ctx& cx, Dir& d, const Penalties& pen, int s) {
     const int32_t* const r_d2 = ring + (su[SU_D2] + kq);
     I4 vo1 = ld4(r_o1), vo2 = ld4(r_o2), vi1 = ld4(r_i1), vi2 = ld4(r_i2);
     I4 vd1 = ld4(r_d1), vd2 = ld4(r_d2), vmis = ld4(ring + (su[SU_MIS] + kq));
+    // chunk-edge neighbours: issued together with the row reads (before the shuffles wait for
+    // those), so a chunk pays one global-memory latency, not two
+    int32_t eL0 = 0, eL1 = 0, eL2 = 0, eL3 = 0, eR0 = 0, eR1 = 0, eR2 = 0, eR3 = 0;
+    if (lane == 0) {
+      eL0 = r_o1[-1];
+      eL1 = r_o2[-1];
+      eL2 = r_i1[-1];
+      eL3 = r_i2[-1];
+    }
+    if (lane == LANES - 1) {
+      eR0 = r_o1[4];
+      eR1 = r_o2[4];
+      eR2 = r_d1[4];
+      eR3 = r_d2[4];
+    }
     int32_t o1L = shfl_up1(vo1.w), o2L = shfl_up1(vo2.w), i1L = shfl_up1(vi1.w), i2L = shfl_up1(vi2.w);
     int32_t o1R = shfl_down1(vo1.x), o2R = shfl_down1(vo2.x), d1R = shfl_down1(vd1.x), d2R = shfl_down1(vd2.x);
     if (lane == 0) {
-      o1L = r_o1[-1];
-      o2L = r_o2[-1];
-      i1L = r_i1[-1];
-      i2L = r_i2[-1];
+      o1L = eL0;
+      o2L = eL1;
+      i1L = eL2;
+      i2L = eL3;
     }
     if (lane == LANES - 1) {
-      o1R = r_o1[4];
-      o2R = r_o2[4];
-      d1R = r_d1[4];
-      d2R = r_d2[4];
+      o1R = eR0;
+      o2R = eR1;
+      d1R = eR2;
+      d2R = eR3;
     }
     const bool interior = kb >= su[SU_INLO] && kb + CH - 1 <= su[SU_INHI];  // warp-uniform
     if (!interior) {
