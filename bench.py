@@ -246,7 +246,7 @@ def main():
     if rank == 0:
         sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    agg = {"align_ms": 0.0, "union_ms": 0.0, "wf_cells": 0, "orient_cells": 0, "unite_ops": 0, "unite_links": 0,
+    agg = {"align_ms": 0.0, "union_ms": 0.0, "orient_ms": 0.0, "wf_cells": 0, "orient_cells": 0, "unite_ops": 0, "unite_links": 0,
            "launches": 0, "aligned_bp": 0, "align_launches": 0, "union_launches": 0}
     step_ms = []
     for k in range(args.steps):
@@ -258,7 +258,7 @@ def main():
         barrier()
         step_ms.append(e0.elapsed_time(e1))
         trace("timed step %d: %.1f ms" % (k, step_ms[-1]))
-        for kk in ("align_ms", "union_ms", "wf_cells", "orient_cells", "unite_ops", "unite_links", "aligned_bp",
+        for kk in ("align_ms", "union_ms", "orient_ms", "wf_cells", "orient_cells", "unite_ops", "unite_links", "aligned_bp",
                    "align_launches", "union_launches"):
             agg[kk] += st[kk]
         agg["launches"] += st["kernel_launches"] + 3  # + uf init, unite_fr_all, (compress/merge counted below)
@@ -318,7 +318,7 @@ def main():
     # = 856.0 GB over the 2.052e10 cells of a 600-pair c2 launch (ncu --set full, profiles/r01g_ncu_align_kernel_c2.txt);
     # scaled by this launch's cell count because the full launch is too long to replay under ncu
     DRAM_BYTES_PER_CELL_NCU = 856.0e9 / 2.052e10
-    alg_bytes = BYTES_PER_CELL * r0_cells + 16 * r0_ocells
+    alg_bytes = BYTES_PER_CELL * r0_cells  # the strand choice runs in its own (small) launch: orient_kernel
     INT_OPS_PER_CELL = 17 + 6  # 17 int ops per cell + 6 per extend word (>= 1 word per cell)
     int_peak = 148 * 4 * 32 * sm_max_mhz * 1e6
     un_s = max(agg["union_ms"] / 1e3, 1e-9)
@@ -343,7 +343,8 @@ def main():
                      "traffic_unit": "bytes per launch (ncu-measured bytes per cell x cells of this launch)",
                      "peak_kind": peak_kind,
                      "algorithmic_bytes_per_launch": alg_bytes / n_launch, "avg_launch_ms": agg["align_ms"] / n_launch,
-                     "share_of_step": agg["align_ms"] / sum(step_ms)},
+                     "share_of_step": agg["align_ms"] / sum(step_ms),
+                     "orient_kernel_share_of_step": agg["orient_ms"] / sum(step_ms)},
         "roofline_int_issue": {"kernel": "align_kernel", "bound": "int_issue",
                                "achieved": INT_OPS_PER_CELL * r0_cells / al_s / 1e9,
                                "peak": int_peak / 1e9, "unit": "Gop/s",

@@ -90,6 +90,7 @@ typedef struct {
   float align_ms;          /* CUDA-event time of the align kernel launches */
   float union_ms;          /* CUDA-event time of the union kernel launches */
   float total_ms;
+  float orient_ms;         /* CUDA-event time of the strand-choice (orient) kernel launches */
 } srgpu_stats;
 
 const char* srgpu_last_error(void);

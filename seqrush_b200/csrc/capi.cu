@@ -72,6 +72,7 @@ struct srgpu_ctx {
   // config
   int threads = 128;
   int ctas_per_sm = 4;
+  bool auto_shape = true;  // launch shape not set by srgpu_ctx_configure: chosen from the sequence length
   int ring_diagonals = 0;
   // sequences
   uint32_t n_seqs = 0;
@@ -97,7 +98,7 @@ struct srgpu_ctx {
   DevBuf<unsigned long long> d_byteoff;
   DevBuf<uint8_t> d_bytes;
   DevBuf<char> d_cigar_str;
-  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   srgpu_stats stats{};
   std::vector<srgpu_uf*> ufs;  // union-finds living on this context (orphaned when it is destroyed)
 };
@@ -151,7 +152,7 @@ extern "C" int srgpu_ctx_create(int device, void* stream, srgpu_ctx** out) {
     CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     c->own_stream = true;
   }
-  for (int i = 0; i < 4; ++i) CK(cudaEventCreate(&c->ev[i]));
+  for (int i = 0; i < 6; ++i) CK(cudaEventCreate(&c->ev[i]));
   *out = c;
   return SRGPU_OK;
 }
@@ -169,7 +170,7 @@ extern "C" void srgpu_ctx_destroy(srgpu_ctx* c) {
   c->d_len.release(); c->d_ring.release(); c->d_full.release(); c->d_orient.release(); c->d_full_meta.release();
   c->d_runs_tmp.release(); c->d_bt_tmp.release(); c->d_pairs.release(); c->d_out.release(); c->d_arena.release();
   c->d_todo.release(); c->d_scalars.release(); c->d_byteoff.release(); c->d_bytes.release(); c->d_cigar_str.release();
-  for (int i = 0; i < 4; ++i) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+  for (int i = 0; i < 6; ++i) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
   if (c->own_stream) cudaStreamDestroy(c->stream);
   delete c;
 }
@@ -190,8 +191,12 @@ extern "C" int srgpu_ctx_configure(srgpu_ctx* c, int threads, int ctas_per_sm, i
       return SRGPU_E_ARG;
     }
     c->threads = threads;
+    c->auto_shape = false;
   }
-  if (ctas_per_sm > 0) c->ctas_per_sm = ctas_per_sm;
+  if (ctas_per_sm > 0) {
+    c->ctas_per_sm = ctas_per_sm;
+    c->auto_shape = false;
+  }
   if (ring_diagonals >= 0) c->ring_diagonals = ring_diagonals;
   return SRGPU_OK;
 }
@@ -417,13 +422,24 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
   }
   const uint32_t maxlen = c->max_len;
   // staged sequences: three packed sequences per CTA in dynamic shared memory when they fit
-  size_t smem = (size_t)3 * c->max_pk_words * 4;
+  // align_kernel stages two packed sequences (chosen query strand, target), orient_kernel three
+  size_t smem = (size_t)2 * c->max_pk_words * 4;
+  size_t smem_orient = (size_t)3 * c->max_pk_words * 4;
   uint32_t smem_seq_words = c->max_pk_words;
+  if (smem_orient > (size_t)c->smem_budget) smem_orient = 0;
   if (smem > (size_t)c->smem_budget) {
     smem = 0;
     smem_seq_words = 0;
   }
-  const int resident = std::min(c->ctas_per_sm, align_occupancy(c->threads, c->ctas_per_sm, smem));
+  // launch shape: 128 threads x 4 CTAs/SM up to ~70 kb; longer sequences have wavefronts wide enough to
+  // keep 8 warps busy per pair and their staged sequences leave room for 2-3 CTAs only (measured on the
+  // 100 kb slice: 256x2 36.9 Mbp/s, 128x4 29.1)
+  int threads = c->threads, ctas_per_sm = c->ctas_per_sm;
+  if (c->auto_shape && maxlen > 70000) {
+    threads = 256;
+    ctas_per_sm = 2;
+  }
+  const int resident = std::min(ctas_per_sm, align_occupancy(threads, ctas_per_sm, smem));
   int grid = c->n_sm * resident;
   if ((uint64_t)grid > n_pairs) grid = (int)n_pairs;
   // workspace geometry
@@ -513,9 +529,25 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
       a.ring_stride = (size_t)2 * pen.scope * 5 * curW;
       a.W = curW;
       a.fixed_w = attempt > 0 ? 1 : 0;
+      if (attempt == 0) {
+        // strand choice of every pair of the chunk (its own launch: three staged sequences)
+        AlignArgs ao = a;
+        ao.smem_seq_words = smem_orient ? c->max_pk_words : 0;
+        CK(cudaMemsetAsync(a.next_pair, 0, sizeof(unsigned int), c->stream));
+        CK(cudaEventRecord(c->ev[4], c->stream));
+        static size_t orient_configured = 0;
+        if (smem_orient > orient_configured) {
+          CK(cudaFuncSetAttribute(orient_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_orient));
+          orient_configured = smem_orient;
+        }
+        orient_kernel<128><<<cur_grid, 128, smem_orient, c->stream>>>(ao);
+        CK(cudaGetLastError());
+        CK(cudaEventRecord(c->ev[5], c->stream));
+        c->stats.kernel_launches++;
+      }
       CK(cudaMemsetAsync(a.next_pair, 0, sizeof(unsigned int), c->stream));
       CK(cudaEventRecord(c->ev[1], c->stream));
-      cudaError_t e = launch_align(a, c->threads, c->ctas_per_sm, cur_grid, smem, c->stream);
+      cudaError_t e = launch_align(a, threads, ctas_per_sm, cur_grid, smem, c->stream);
       if (e != cudaSuccess) {
         g_err = std::string("align_kernel launch: ") + cudaGetErrorString(e);
         return SRGPU_E_CUDA;
@@ -529,6 +561,10 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
       float ms = 0;
       CK(cudaEventElapsedTime(&ms, c->ev[1], c->ev[2]));
       c->stats.align_ms += ms;
+      if (attempt == 0) {
+        CK(cudaEventElapsedTime(&ms, c->ev[4], c->ev[5]));
+        c->stats.orient_ms += ms;
+      }
       // unite what this launch produced (records of failed pairs are skipped by the kernel)
       if ((rc = do_union(first, a.todo, a.n_pairs))) return rc;
       // pairs that need a wider ring or did not fit the arena (rare) are re-run

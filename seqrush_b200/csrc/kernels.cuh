@@ -149,9 +149,70 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// ---------------------------------------------------------------------------
+// Strand choice for every pair of a launch (allwave/src/alignment.rs:24-30,148-171), one pair per
+// CTA, persistent CTAs. It runs as its own launch because it needs three staged sequences (query
+// forward, query reverse complement, target) while the aligner needs two: keeping it out of
+// align_kernel cuts that kernel's shared memory per CTA by a third (more resident CTAs for long
+// sequences) and its instruction footprint. Writes is_reverse / edit_distance / ocells of out[pi].
+// ---------------------------------------------------------------------------
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS) orient_kernel(AlignArgs a) {
+  extern __shared__ __align__(16) uint32_t s_seq[];  // [Pf | Pr | T], smem_seq_words each
+  __shared__ CtaShared sh;
+  __shared__ unsigned int s_pair;
+  __shared__ __align__(8) uint64_t s_bar;
+  Ctx cx;
+  cx.sh = &sh;
+  cx.tid = threadIdx.x;
+  cx.nt = THREADS;
+  cx.parity = 0;
+  int32_t* obuf = a.orient + (size_t)blockIdx.x * a.orient_stride;
+  const int lbits = a.seqs.lbits;
+  const bool staged = a.smem_seq_words != 0;
+  uint32_t phase = 0;
+  if (staged && threadIdx.x == 0) mbar_init(&s_bar, 1);
+  while (true) {
+    __syncthreads();
+    if (threadIdx.x == 0) s_pair = atomicAdd(a.next_pair, 1u);
+    __syncthreads();
+    const unsigned int slot = s_pair;
+    if (slot >= a.n_pairs) break;
+    const unsigned int pi = a.todo ? a.todo[slot] : slot;
+    const uint2 pr = a.pairs[pi];
+    const uint32_t plen = a.seqs.len[pr.x], tlen = a.seqs.len[pr.y];
+    const uint32_t* Pf = a.seqs.pk_fwd + a.seqs.pk_off[pr.x];
+    const uint32_t* Pr = a.seqs.pk_rc + a.seqs.pk_off[pr.x];
+    const uint32_t* T = a.seqs.pk_fwd + a.seqs.pk_off[pr.y];
+    if (staged) {
+      const uint32_t wp = 8 + (((((plen << lbits) + 31) >> 5) + 3) & ~3u);
+      const uint32_t wt = 8 + (((((tlen << lbits) + 31) >> 5) + 3) & ~3u);
+      if (threadIdx.x == 0) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        mbar_expect_tx(&s_bar, (2 * wp + wt) * 4);
+        bulk_g2s(s_seq, Pf - 4, wp * 4, &s_bar);
+        bulk_g2s(s_seq + a.smem_seq_words, Pr - 4, wp * 4, &s_bar);
+        bulk_g2s(s_seq + 2 * a.smem_seq_words, T - 4, wt * 4, &s_bar);
+      }
+      mbar_wait(&s_bar, phase);
+      phase ^= 1;
+      Pf = s_seq + 4;
+      Pr = s_seq + a.smem_seq_words + 4;
+      T = s_seq + 2 * a.smem_seq_words + 4;
+    }
+    const OrientResult orr = wf_orient(cx, Pf, Pr, T, lbits, (int)plen, (int)tlen, obuf, a.orient_row);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      a.out[pi].is_reverse = orr.is_reverse;
+      a.out[pi].edit_distance = (uint32_t)orr.distance;
+      a.out[pi].ocells = sh.ocells;
+    }
+  }
+}
+
 template <int THREADS, int MIN_CTAS>
 __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
-  extern __shared__ __align__(16) uint32_t s_seq[];  // [Pf | Pr | T], smem_seq_words each
+  extern __shared__ __align__(16) uint32_t s_seq[];  // [query strand chosen by orient_kernel | target], smem_seq_words each
   __shared__ CtaShared sh;
   __shared__ unsigned int s_pair;
   __shared__ unsigned int s_cnt[8];
@@ -172,7 +233,6 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
   ro.cap = a.runs_cap;
   ro.bt = a.bt_tmp + b * (size_t)a.runs_cap;
   ro.bt_cap = a.runs_cap;
-  int32_t* obuf = a.orient + b * a.orient_stride;
   const int lbits = a.seqs.lbits;
   const bool staged = a.smem_seq_words != 0;
   uint32_t phase = 0;
@@ -191,33 +251,30 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
     const unsigned int pi = a.todo ? a.todo[slot] : slot;
     const uint2 pr = a.pairs[pi];
     const uint32_t plen = a.seqs.len[pr.x], tlen = a.seqs.len[pr.y];
-    const uint32_t* Pf = a.seqs.pk_fwd + a.seqs.pk_off[pr.x];
-    const uint32_t* Pr = a.seqs.pk_rc + a.seqs.pk_off[pr.x];
+    // 1. strand: chosen by orient_kernel (allwave/src/alignment.rs:24-30)
+    OrientResult orr;
+    orr.is_reverse = a.out[pi].is_reverse;
+    orr.distance = (int)a.out[pi].edit_distance;
+    const unsigned long long pair_ocells = a.out[pi].ocells;
+    const uint32_t* P = (orr.is_reverse ? a.seqs.pk_rc : a.seqs.pk_fwd) + a.seqs.pk_off[pr.x];
     const uint32_t* T = a.seqs.pk_fwd + a.seqs.pk_off[pr.y];
     if (staged) {
-      // stage the three packed sequences (with their guard words) into shared memory
+      // stage the two packed sequences (with their guard words) into shared memory
       const uint32_t wp = 8 + (((((plen << lbits) + 31) >> 5) + 3) & ~3u);
       const uint32_t wt = 8 + (((((tlen << lbits) + 31) >> 5) + 3) & ~3u);
       if (threadIdx.x == 0) {
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        mbar_expect_tx(&s_bar, (2 * wp + wt) * 4);
-        bulk_g2s(s_seq, Pf - 4, wp * 4, &s_bar);
-        bulk_g2s(s_seq + a.smem_seq_words, Pr - 4, wp * 4, &s_bar);
-        bulk_g2s(s_seq + 2 * a.smem_seq_words, T - 4, wt * 4, &s_bar);
+        mbar_expect_tx(&s_bar, (wp + wt) * 4);
+        bulk_g2s(s_seq, P - 4, wp * 4, &s_bar);
+        bulk_g2s(s_seq + a.smem_seq_words, T - 4, wt * 4, &s_bar);
       }
       mbar_wait(&s_bar, phase);
       phase ^= 1;
-      Pf = s_seq + 4;
-      Pr = s_seq + a.smem_seq_words + 4;
-      T = s_seq + 2 * a.smem_seq_words + 4;
+      P = s_seq + 4;
+      T = s_seq + a.smem_seq_words + 4;
     }
-    // 1. strand (allwave/src/alignment.rs:24-30)
 #ifdef WFA_PROFILE
-    const long long t_or0 = clock64();
-#endif
-    const OrientResult orr = wf_orient(cx, Pf, Pr, T, lbits, (int)plen, (int)tlen, obuf, a.orient_row);
-#ifdef WFA_PROFILE
-    const long long t_or1 = clock64();
+    const long long t_or0 = clock64(), t_or1 = t_or0;
 #endif
     // 2. BiWFA (allwave/src/alignment.rs:189-276). Ring rows are sized from the edit distance just
     //    found (penalty <= 10 per edit, about half of it per direction); a pair that still
@@ -230,7 +287,7 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
     ws.W = W;
     ws.ring_r = ws.ring_f + (size_t)a.pen.scope * 5 * W;
     SeqView sv;
-    sv.p = orr.is_reverse ? Pr : Pf;
+    sv.p = P;
     sv.t = T;
     sv.lbits = lbits;
     // an alignment with `distance` unit edits costs at most max(x, cheapest one-base gap) per edit
@@ -308,7 +365,7 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
       o.n_runs = (st == ST_OK) ? r.n_runs : 0;
       o.run_off = off;
       o.cells = sh.cells;
-      o.ocells = sh.ocells;
+      o.ocells = pair_ocells;
       a.out[pi] = o;
     }
   }
