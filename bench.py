@@ -154,10 +154,26 @@ def run_reference(args):
                                    "reference WFA2-lib + edlib compiled from its sources + restated Rust glue" % sample},
         "e2e": {"value": val, "unit": "Mbp/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(out))
+    emit(out)
+
+
+_JSON_OUT = None
+
+
+def emit(obj):
+    """The one JSON line of the contract, on the process's original stdout."""
+    f = _JSON_OUT or sys.stdout
+    f.write(json.dumps(obj) + "\n")
+    f.flush()
 
 
 def main():
+    # stdout carries exactly one JSON line: anything else a library prints there (the NCCL version
+    # banner, device printf) is sent to stderr by pointing fd 1 at fd 2 and keeping the original
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
@@ -190,8 +206,6 @@ def main():
     dist = None
     if world > 1:
         import torch.distributed as dist
-        # stdout carries exactly one JSON line: NCCL's own banner / debug lines go to stderr
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
         trace("process group up")
 
@@ -365,7 +379,7 @@ def main():
                                "sample": "%d random ordered pairs of the workload, oracle/_ref (reference WFA2-lib + "
                                          "edlib compiled from its sources) + restated Rust glue, %d threads" % (ns, cores),
                                "unite_ops_per_s": st["unite_calls"] / st["seconds"]}
-    print(json.dumps(out))
+    emit(out)
     if dist is not None:
         dist.destroy_process_group()
 
