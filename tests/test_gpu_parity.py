@@ -178,6 +178,10 @@ def test_union_find_kats(s):
     assert uf.find(9) == 9
     uf.unite_fr_all(500)
     assert uf.same(4, 5) and uf.count_components(500) <= 500
+    # UFRush::clear (uf_rush lib.rs:211-216): every Pos is its own set again
+    uf.clear()
+    assert not uf.same(2, 600) and not uf.same(4, 5) and uf.find(600) == 600
+    assert uf.count_components(500) == 500
     ctx.close()
 
 

@@ -67,3 +67,20 @@ def test_synth_is_deterministic():
     b = synth.make_config("c2", n=3, length=2000)[1]
     assert all(np.array_equal(x, y) for x, y in zip(a, b))
     assert all(set(np.unique(x).tolist()) <= set(b"ACGT") for x in a)
+
+
+def test_bench_reference_arm_prints_one_json_line():
+    """bench.py contract: exactly one JSON line on stdout (library banners must not land there)."""
+    import json, os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if not os.path.exists(os.path.join(root, "oracle", "_ref", "libsrref_generic.so")):
+        pytest.skip("oracle/_ref not built")
+    r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0",
+                        "--cpu-sample", "2", "--workload", "tiny"], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True,
+                       timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [ln for ln in r.stdout.splitlines() if ln.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["cpu_baseline"]["kind"] == "reference" and d["value"] > 0
+    assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["unit"] == "Mbp/s"
