@@ -577,7 +577,13 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
         if (st == ST_WS_DIAG_OVERFLOW) { again.push_back(i); diag = true; }
         else if (st == ST_ARENA_OVERFLOW) { again.push_back(i); arena_over = true; }
       }
-      if (again.empty() || attempt >= 3) break;
+      if (again.empty()) break;
+      // every retry completes the pairs that fit (the arena is reused, the ring gets its full width), so
+      // the list shrinks; a list that stops shrinking means a pair cannot be served at all: fail loudly
+      if (attempt >= 2 && again.size() >= cnt) {
+        g_err = "pairs do not fit the alignment workspace (ring width / CIGAR arena) after retries";
+        return SRGPU_E_INTERNAL;
+      }
       if (keep_runs && arena_over) {
         g_err = "CIGAR arena overflow: align fewer pairs per call";
         return SRGPU_E_INTERNAL;

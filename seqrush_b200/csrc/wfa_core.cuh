@@ -156,6 +156,7 @@ struct CtaShared {
   int ovl[MAX_SCOPE * 5];  // overlap search results (min k_0 per task)
   int wsetup[16][16];      // per warp: row offsets and interior bounds of the running score step
   int chunk_ctr;           // next unclaimed chunk of the running score step (dynamic balance)
+  int end_val;             // offset of the end cell (diagonal tlen-plen, end component) written by the vector step
   Frame stack[STACK_MAX];
   int sp;
   Breakpoint bp;
@@ -489,7 +490,8 @@ WFA_FN void publish_comp(const WfStore& st, const RedSlots* red, const StepCtl& 
   }
 }
 
-WFA_FN void step_finish(Ctx& cx, const Dir& d, const StepCtl& t, const int* mn, const int* mx, int max_ak, StepOut& o) {
+WFA_FN void step_finish(Ctx& cx, const Dir& d, const StepCtl& t, const int* mn, const int* mx, int max_ak, StepOut& o,
+                        bool end_stashed) {
   const WfStore& st = d.st;
   RedSlots* red = &cx.sh->red[cx.parity];
   max_ak = warp_max(max_ak);
@@ -548,7 +550,10 @@ WFA_FN void step_finish(Ctx& cx, const Dir& d, const StepCtl& t, const int* mn, 
     const bool al = ce == C_M ? true : ce == C_I1 ? t.a_i1 : ce == C_I2 ? t.a_i2 : ce == C_D1 ? t.a_d1 : t.a_d2;
     const bool present = al && red->mn[ce] <= red->mx[ce];
     if (present && red->mn[ce] <= ak && ak <= red->mx[ce]) {
-      if (st.row(t.s, ce)[ak] >= d.tlen) o.end_reached = 1;
+      // the vector step leaves the end cell in shared memory (a global read here would sit on the
+      // critical path of every step)
+      const int32_t ev = end_stashed ? cx.sh->end_val : st.row(t.s, ce)[ak];
+      if (ev >= d.tlen) o.end_reached = 1;
     }
   }
   cx.parity ^= 1;
@@ -727,7 +732,7 @@ WFA_FN StepOut wf_step(Ctx& cx, Dir& d, const Penalties& pen, int s) {
   ctl.a_d2 = a_d2;
   const int mns[5] = {sp0.mn, sp1.mn, sp2.mn, sp3.mn, sp4.mn};
   const int mxs[5] = {sp0.mx, sp1.mx, sp2.mx, sp3.mx, sp4.mx};
-  step_finish(cx, d, ctl, mns, mxs, max_ak, o);
+  step_finish(cx, d, ctl, mns, mxs, max_ak, o, false);
   return o;
 }
 
@@ -1122,6 +1127,17 @@ WFA_FN StepOut wf_step_vec(Ctx& cx, Dir& d, const Penalties& pen, int s) {
       }
     }
     if (lane_act) st4(ring + (su[SU_WM] + k0), mx[0], mx[1], mx[2], mx[3]);
+    {
+      // end cell of this search (WFA/wavefront_termination.c:37-113) for the test in step_finish
+      const unsigned je = (unsigned)(d.tlen - d.plen - k0);
+      if (je < 4u) {
+        const int ce = d.cend;
+#define SEL4(a) (je == 0 ? a[0] : je == 1 ? a[1] : je == 2 ? a[2] : a[3])
+        const int32_t e_m = SEL4(mx), e_i1 = SEL4(ins1), e_i2 = SEL4(ins2), e_d1 = SEL4(del1), e_d2 = SEL4(del2);
+#undef SEL4
+        cx.sh->end_val = ce == C_M ? e_m : ce == C_I1 ? e_i1 : ce == C_I2 ? e_i2 : ce == C_D1 ? e_d1 : e_d2;
+      }
+    }
 #ifdef WFA_PROFILE
     if (cx.tid == 32 && interior) {
       const long long tc2 = clock64();
@@ -1156,7 +1172,7 @@ WFA_FN StepOut wf_step_vec(Ctx& cx, Dir& d, const Penalties& pen, int s) {
   ctl.a_d2 = a_d2;
   const int mns[5] = {sp0.mn, sp1.mn, sp2.mn, sp3.mn, sp4.mn};
   const int mxs[5] = {sp0.mx, sp1.mx, sp2.mx, sp3.mx, sp4.mx};
-  step_finish(cx, d, ctl, mns, mxs, max_ak, o);
+  step_finish(cx, d, ctl, mns, mxs, max_ak, o, true);
 #ifdef WFA_PROFILE
   if (cx.tid == 0) {
     const long long t6 = clock64();
