@@ -329,9 +329,9 @@ def main():
     n_launch = max(1, agg["align_launches"])
     BYTES_PER_CELL = 48  # 7 source offsets read + 5 offsets written, int32 (DESIGN.md "roofline")
     # measured DRAM traffic of the align kernel per wavefront cell: dram__bytes_read.sum + dram__bytes_write.sum
-    # = 856.0 GB over the 2.052e10 cells of a 600-pair c2 launch (ncu --set full, profiles/r01g_ncu_align_kernel_c2.txt);
+    # = 855.5 GB over the 2.052e10 cells of a 600-pair c2 launch (ncu --set full, profiles/r01j_ncu_align_kernel_c2.txt);
     # scaled by this launch's cell count because the full launch is too long to replay under ncu
-    DRAM_BYTES_PER_CELL_NCU = 856.0e9 / 2.052e10
+    DRAM_BYTES_PER_CELL_NCU = 855.5e9 / 2.052e10
     alg_bytes = BYTES_PER_CELL * r0_cells  # the strand choice runs in its own (small) launch: orient_kernel
     INT_OPS_PER_CELL = 17 + 6  # 17 int ops per cell + 6 per extend word (>= 1 word per cell)
     int_peak = 148 * 4 * 32 * sm_max_mhz * 1e6
