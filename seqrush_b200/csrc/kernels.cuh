@@ -374,8 +374,8 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
     const unsigned long long* pf = sh.prof;
     const double n = pf[0] ? (double)pf[0] : 1.0;
     printf("[prof cta %d] ring steps %llu  total cyc %lld | per step: top-barrier %.0f  setup %.0f  loop %.0f  finish %.0f  "
-           "| avg width %.0f\n",
-           (int)blockIdx.x, pf[0], clock64() - prof_start, pf[1] / n, pf[2] / n, pf[3] / n, pf[4] / n, pf[7] / n);
+           "(barrier wait %.0f) | avg width %.0f\n",
+           (int)blockIdx.x, pf[0], clock64() - prof_start, pf[1] / n, pf[2] / n, pf[3] / n, pf[4] / n, pf[5] / n, pf[7] / n);
     printf("[prof cta %d] strand choice %llu cyc (sum of edit distances %llu), BiWFA %llu cyc\n", (int)blockIdx.x, pf[13], pf[15], pf[14]);
     printf("[prof cta %d] warp1 interior chunks %llu: compute %.0f cyc, extend %.0f cyc | warp0 fringe chunks %llu: %.0f cyc\n",
            (int)blockIdx.x, pf[8], pf[9] / (pf[8] ? (double)pf[8] : 1.0), pf[10] / (pf[8] ? (double)pf[8] : 1.0), pf[11],

@@ -519,7 +519,13 @@ WFA_FN void step_finish(Ctx& cx, const Dir& d, const StepCtl& t, const int* mn, 
     }
   }
 #endif
+#ifdef WFA_PROFILE
+  const long long tb0 = clock64();
+#endif
   cta_sync();
+#ifdef WFA_PROFILE
+  if (cx.tid == 0) cx.sh->prof[5] += clock64() - tb0;  // wait at the closing barrier
+#endif
   o.max_ak = red->max_ak;
 #if WFA_DEVICE
   if (cx.tid < 5) {
