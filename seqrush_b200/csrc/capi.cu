@@ -355,7 +355,7 @@ static int check_penalties(const srgpu_penalties* p, Penalties* out) {
   out->o2 = p->gap_open2;
   out->e2 = p->gap_ext2;
   out->scope = std::max(std::max(p->gap_open1 + p->gap_ext1, p->gap_open2 + p->gap_ext2), p->mismatch) + 1;
-  if (out->scope > MAX_SCOPE) {
+  if (out->scope + 1 > MAX_SCOPE) {
     g_err = "penalties too large: max_score_scope exceeds the ring depth (64)";
     return SRGPU_E_ARG;
   }
@@ -524,9 +524,9 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
     int cur_grid = std::min<int>(grid, (int)cn);
     CK(cudaMemsetAsync(c->d_scalars.p, 0, 2 * sizeof(unsigned long long), c->stream));
     for (int attempt = 0;; ++attempt) {
-      if ((rc = c->d_ring.ensure((size_t)cur_grid * 2 * pen.scope * 5 * curW))) return rc;
+      if ((rc = c->d_ring.ensure((size_t)cur_grid * 2 * (pen.scope + 1) * 5 * curW))) return rc;
       a.ring = c->d_ring.p;
-      a.ring_stride = (size_t)2 * pen.scope * 5 * curW;
+      a.ring_stride = (size_t)2 * (pen.scope + 1) * 5 * curW;
       a.W = curW;
       a.fixed_w = attempt > 0 ? 1 : 0;
       if (attempt == 0) {
@@ -593,7 +593,7 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
       if (diag) curW = (fullW + 63) & ~63;
       cur_grid = std::min<int>(cur_grid, (int)todo.size());
       {  // keep the retry ring within ~24 GB
-        const size_t per = (size_t)2 * pen.scope * 5 * curW * sizeof(int32_t);
+        const size_t per = (size_t)2 * (pen.scope + 1) * 5 * curW * sizeof(int32_t);
         const size_t maxg = std::max<size_t>(1, ((size_t)24 << 30) / per);
         cur_grid = (int)std::min<size_t>((size_t)cur_grid, maxg);
       }

@@ -89,7 +89,7 @@ struct AlignArgs {
   Penalties pen;
   // per-CTA workspace (indexed by blockIdx.x)
   int32_t* ring;
-  size_t ring_stride;  // ints per CTA = 2*scope*5*W
+  size_t ring_stride;  // ints per CTA = 2*(scope+1)*5*W
   int W;               // widest ring row this launch can address
   int fixed_w;         // 1: every pair uses W (retry launches); 0: rows are sized per pair from its edit distance
   int32_t* full;
@@ -285,7 +285,7 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
       if (est < W) W = (int)est;
     }
     ws.W = W;
-    ws.ring_r = ws.ring_f + (size_t)a.pen.scope * 5 * W;
+    ws.ring_r = ws.ring_f + (size_t)(a.pen.scope + 1) * 5 * W;
     SeqView sv;
     sv.p = P;
     sv.t = T;

@@ -154,9 +154,9 @@ struct CtaShared {
   int ub_r[MAX_SCOPE * 5];
   RedSlots red[2];
   int ovl[MAX_SCOPE * 5];  // overlap search results (min k_0 per task)
-  int wsetup[16][16];      // per warp: row offsets and interior bounds of the running score step
+  int ds[2][48];           // per direction: limits, interior bounds, row offsets, flags of the running score step
   int chunk_ctr;           // next unclaimed chunk of the running score step (dynamic balance)
-  int end_val;             // offset of the end cell (diagonal tlen-plen, end component) written by the vector step
+  int end_val[2];          // per direction: offset of the end cell (diagonal tlen-plen, end component)
   Frame stack[STACK_MAX];
   int sp;
   Breakpoint bp;
@@ -558,7 +558,7 @@ WFA_FN void step_finish(Ctx& cx, const Dir& d, const StepCtl& t, const int* mn, 
     if (present && red->mn[ce] <= ak && ak <= red->mx[ce]) {
       // the vector step leaves the end cell in shared memory (a global read here would sit on the
       // critical path of every step)
-      const int32_t ev = end_stashed ? cx.sh->end_val : st.row(t.s, ce)[ak];
+      const int32_t ev = end_stashed ? cx.sh->end_val[0] : st.row(t.s, ce)[ak];
       if (ev >= d.tlen) o.end_reached = 1;
     }
   }
@@ -833,17 +833,32 @@ struct Span4 {
   }
 };
 
-WFA_FN StepOut wf_step_vec(Ctx& cx, Dir& d, const Penalties& pen, int s) {
-  StepOut o;
-  o.null_step = 0;
-  o.end_reached = 0;
-  o.max_ak = 0;
-  o.overflow = 0;
-  d.st.set_cur(s);
-  PROF_T(t0);
-  cta_sync();
-  PROF_T(t1);
+// ---------------------------------------------------------------------------
+// Score step of the breakpoint search for ONE or BOTH directions at once ("dual step").
+// The forward step to score sf and the reverse step to score sr do not depend on each other, so
+// while the two searches are far apart they share one pass: their chunks go into one claim pool
+// for all warps of the CTA (one copy of the chunk code: the direction is a run-time parameter read
+// from shared memory), which halves the barriers, setups and publishes per score and evens out
+// the work of the warps. Phases:
+//   A barrier            rows and metas of earlier steps are visible
+//   B setup              warp (dir % nwarps) derives limits, interior, row offsets of direction dir
+//                        into sh->ds[dir], clears that direction's trim slots and the chunk counter
+//   C barrier
+//   D chunk loop         as before; the trims of a chunk go to shared memory right away
+//   E barrier
+//   F publish            five lanes per direction write the metas; every thread reads the results
+// ---------------------------------------------------------------------------
+enum {
+  DS_O1 = 0, DS_O2, DS_I1, DS_I2, DS_D1, DS_D2, DS_MIS, DS_WM, DS_WI1, DS_WI2, DS_WD1, DS_WD2,
+  DS_INLO, DS_INHI, DS_LO, DS_HI, DS_LOAL, DS_NCH, DS_FLAGS, DS_META,  // DS_META .. +13: seven (lo, hi) pairs
+  DS_P0 = DS_META + 14, DS_T0, DS_REV, DS_CEND, DS_NULL, DS_OVF, DS_WIDTH, DS_SLOT5, DS_S, DS_SO1, DS_SE1, DS_SO2, DS_SE2,
+  DS_NFLAGS, DS_WORDS
+};
+
+// phase B for one direction; executed by one whole warp (lane 0 writes)
+WFA_FN void wf_setup_dir(Ctx& cx, const Dir& d, const Penalties& pen, int s, int dir, int base_adj, int lane) {
   const WfStore& st = d.st;
+  int* ds = cx.sh->ds[dir];
   const int s_mis = s - pen.x, s_o1 = s - pen.o1 - pen.e1, s_e1 = s - pen.e1;
   const int s_o2 = s - pen.o2 - pen.e2, s_e2 = s - pen.e2;
   const WfMeta m_mis = st.get(s_mis, C_M), m_o1 = st.get(s_o1, C_M), m_o2 = st.get(s_o2, C_M);
@@ -852,17 +867,34 @@ WFA_FN StepOut wf_step_vec(Ctx& cx, Dir& d, const Penalties& pen, int s) {
   const bool n_mis = m_mis.lo > m_mis.hi, n_o1 = m_o1.lo > m_o1.hi, n_o2 = m_o2.lo > m_o2.hi;
   const bool n_i1 = m_i1.lo > m_i1.hi, n_d1 = m_d1.lo > m_d1.hi, n_i2 = m_i2.lo > m_i2.hi, n_d2 = m_d2.lo > m_d2.hi;
   const int slot5 = st.slot(s) * 5;
-  if (n_mis && n_o1 && n_o2 && n_i1 && n_d1 && n_i2 && n_d2) {
-    if (cx.tid == 0) {
-      for (int c = 0; c < 5; ++c) {
-        st.meta[slot5 + c].lo = 1;
-        st.meta[slot5 + c].hi = -1;
-        st.ub[slot5 + c] = UB_NONE;
-      }
-    }
-    o.null_step = 1;
-    return o;
+  // trim slots of this direction start clean (lanes 0..10), end-cell stash too
+#if WFA_DEVICE
+  if (lane < 11) (&cx.sh->red[dir].mn[0])[lane] = lane < 5 ? INT32_MAX : lane < 10 ? INT32_MIN : 0;
+#else
+  for (int c = 0; c < 5; ++c) {
+    cx.sh->red[dir].mn[c] = INT32_MAX;
+    cx.sh->red[dir].mx[c] = INT32_MIN;
   }
+  cx.sh->red[dir].max_ak = 0;
+#endif
+  if (lane != 0) return;
+  ds[DS_NULL] = 0;
+  ds[DS_OVF] = 0;
+  ds[DS_NCH] = 0;
+  ds[DS_WIDTH] = 0;
+  ds[DS_S] = s;
+  ds[DS_SLOT5] = slot5;
+  if (n_mis && n_o1 && n_o2 && n_i1 && n_d1 && n_i2 && n_d2) {
+    // null step (WFA/wavefront_compute_affine2p.c:343-353)
+    for (int c = 0; c < 5; ++c) {
+      st.meta[slot5 + c].lo = 1;
+      st.meta[slot5 + c].hi = -1;
+      st.ub[slot5 + c] = UB_NONE;
+    }
+    ds[DS_NULL] = 1;
+    return;
+  }
+  // limits (WFA/wavefront_compute.c:40-86); null inputs carry lo=1,hi=-1 like the reference's null wavefront
   int lo = m_mis.lo, hi = m_mis.hi;
   lo = imin(lo, m_o1.lo - 1);
   hi = imax(hi, m_o1.hi + 1);
@@ -878,10 +910,9 @@ WFA_FN StepOut wf_step_vec(Ctx& cx, Dir& d, const Penalties& pen, int s) {
   hi = imax(hi, m_d2.hi - 1);
   // keep 8 diagonals of slack on both sides: aligned 4-wide accesses may touch [lo-3, hi+3]
   if (lo <= -(st.W >> 1) + 8 || hi >= (st.W >> 1) - 8) {
-    o.overflow = 1;
-    return o;
+    ds[DS_OVF] = 1;
+    return;
   }
-  if (cx.tid == 0) cx.sh->cells += (unsigned long long)(hi - lo + 1);
   const bool a_i1 = !n_o1 || !n_i1, a_d1 = !n_o1 || !n_d1, a_i2 = !n_o2 || !n_i2, a_d2 = !n_o2 || !n_d2;
   int in_lo = 1, in_hi = 0;
   if (!(n_mis || n_o1 || n_o2 || n_i1 || n_d1 || n_i2 || n_d2)) {
@@ -890,14 +921,62 @@ WFA_FN StepOut wf_step_vec(Ctx& cx, Dir& d, const Penalties& pen, int s) {
     in_lo = imax(in_lo, lo);
     in_hi = imin(in_hi, hi);
   }
-  const uint32_t tlen = (uint32_t)d.tlen, plen = (uint32_t)d.plen;
-  Span4 sp0, sp1, sp2, sp3, sp4;
-  sp0.init();
-  sp1.init();
-  sp2.init();
-  sp3.init();
-  sp4.init();
-  int max_ak = 0;
+  const int lo_al = lo & ~3;  // arithmetic: rounds towards -inf on two's complement
+  ds[DS_O1] = base_adj + st.off_of(s_o1 < 0 ? 0 : s_o1, C_M);
+  ds[DS_O2] = base_adj + st.off_of(s_o2 < 0 ? 0 : s_o2, C_M);
+  ds[DS_I1] = base_adj + st.off_of(s_e1 < 0 ? 0 : s_e1, C_I1);
+  ds[DS_I2] = base_adj + st.off_of(s_e2 < 0 ? 0 : s_e2, C_I2);
+  ds[DS_D1] = base_adj + st.off_of(s_e1 < 0 ? 0 : s_e1, C_D1);
+  ds[DS_D2] = base_adj + st.off_of(s_e2 < 0 ? 0 : s_e2, C_D2);
+  ds[DS_MIS] = base_adj + st.off_of(s_mis < 0 ? 0 : s_mis, C_M);
+  ds[DS_WM] = base_adj + st.off_of(s, C_M);
+  ds[DS_WI1] = base_adj + st.off_of(s, C_I1);
+  ds[DS_WI2] = base_adj + st.off_of(s, C_I2);
+  ds[DS_WD1] = base_adj + st.off_of(s, C_D1);
+  ds[DS_WD2] = base_adj + st.off_of(s, C_D2);
+  ds[DS_INLO] = in_lo;
+  ds[DS_INHI] = in_hi;
+  ds[DS_LO] = lo;
+  ds[DS_HI] = hi;
+  ds[DS_LOAL] = lo_al;
+  ds[DS_NCH] = (hi - lo_al) / (LANES * 4) + 1;
+  ds[DS_WIDTH] = hi - lo + 1;
+  ds[DS_FLAGS] = (a_i1 ? 1 : 0) | (a_i2 ? 2 : 0) | (a_d1 ? 4 : 0) | (a_d2 ? 8 : 0);
+  ds[DS_NFLAGS] = (n_o1 ? 1 : 0) | (n_o2 ? 2 : 0) | (n_i1 ? 4 : 0) | (n_d1 ? 8 : 0) | (n_i2 ? 16 : 0) | (n_d2 ? 32 : 0);
+  ds[DS_META + 0] = m_o1.lo;
+  ds[DS_META + 1] = m_o1.hi;
+  ds[DS_META + 2] = m_o2.lo;
+  ds[DS_META + 3] = m_o2.hi;
+  ds[DS_META + 4] = m_i1.lo;
+  ds[DS_META + 5] = m_i1.hi;
+  ds[DS_META + 6] = m_i2.lo;
+  ds[DS_META + 7] = m_i2.hi;
+  ds[DS_META + 8] = m_d1.lo;
+  ds[DS_META + 9] = m_d1.hi;
+  ds[DS_META + 10] = m_d2.lo;
+  ds[DS_META + 11] = m_d2.hi;
+  ds[DS_META + 12] = m_mis.lo;
+  ds[DS_META + 13] = m_mis.hi;
+  ds[DS_P0] = d.p0;
+  ds[DS_T0] = d.t0;
+  ds[DS_REV] = d.reverse;
+  ds[DS_CEND] = d.cend;
+  ds[DS_SO1] = s_o1;
+  ds[DS_SE1] = s_e1;
+  ds[DS_SO2] = s_o2;
+  ds[DS_SE2] = s_e2;
+}
+
+struct StepOut2 {
+  StepOut f, r;
+};
+
+WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, int sf, int sr, bool run_f, bool run_r) {
+  StepOut2 out;
+  out.f.null_step = out.f.end_reached = out.f.max_ak = out.f.overflow = 0;
+  out.r = out.f;
+  if (run_f) df.st.set_cur(sf);
+  if (run_r) dr.st.set_cur(sr);
   const int lane = lane_id();
 #if WFA_DEVICE
   const int warp = cx.tid >> 5, nwarps = cx.nt >> 5;
@@ -905,43 +984,78 @@ WFA_FN StepOut wf_step_vec(Ctx& cx, Dir& d, const Penalties& pen, int s) {
   const int warp = 0, nwarps = 1;
 #endif
   constexpr int CH = LANES * 4;
-  // Row offsets (elements from the ring base) and the interior bounds go through a small per-warp
-  // area of shared memory: the chunk loop re-reads them instead of holding 24 pointer registers
-  // (which the compiler otherwise rematerialises from the kernel arguments in every chunk).
-  enum { SU_O1 = 0, SU_O2, SU_I1, SU_I2, SU_D1, SU_D2, SU_MIS, SU_WM, SU_WI1, SU_WI2, SU_WD1, SU_WD2, SU_INLO, SU_INHI };
-  int* su_w = cx.sh->wsetup[warp];
-  if (lane == 0) {
-    su_w[SU_O1] = st.off_of(s_o1 < 0 ? 0 : s_o1, C_M);
-    su_w[SU_O2] = st.off_of(s_o2 < 0 ? 0 : s_o2, C_M);
-    su_w[SU_I1] = st.off_of(s_e1 < 0 ? 0 : s_e1, C_I1);
-    su_w[SU_I2] = st.off_of(s_e2 < 0 ? 0 : s_e2, C_I2);
-    su_w[SU_D1] = st.off_of(s_e1 < 0 ? 0 : s_e1, C_D1);
-    su_w[SU_D2] = st.off_of(s_e2 < 0 ? 0 : s_e2, C_D2);
-    su_w[SU_MIS] = st.off_of(s_mis < 0 ? 0 : s_mis, C_M);
-    su_w[SU_WM] = st.off_of(s, C_M);
-    su_w[SU_WI1] = st.off_of(s, C_I1);
-    su_w[SU_WI2] = st.off_of(s, C_I2);
-    su_w[SU_WD1] = st.off_of(s, C_D1);
-    su_w[SU_WD2] = st.off_of(s, C_D2);
-    su_w[SU_INLO] = in_lo;
-    su_w[SU_INHI] = in_hi;
+  PROF_T(t0);
+  cta_sync();  // A
+  PROF_T(t1);
+  // B
+  if (run_f && warp == 0) wf_setup_dir(cx, df, pen, sf, 0, 0, lane);
+  if (run_r && warp == (1 % nwarps)) wf_setup_dir(cx, dr, pen, sr, 1, (int)(dr.st.base - df.st.base), lane);
+  if (cx.tid == 0) {
+    cx.sh->chunk_ctr = 0;
+    if (!run_f) cx.sh->ds[0][DS_NCH] = 0;
+    if (!run_r) cx.sh->ds[1][DS_NCH] = 0;
   }
-#if WFA_DEVICE
-  __syncwarp();
-#endif
-  const volatile int* su = su_w;
-  int32_t* ring = st.base;
+  cta_sync();  // C
+  PROF_T(t2);
+  {
+    const volatile int* s0 = cx.sh->ds[0];
+    const volatile int* s1 = cx.sh->ds[1];
+    if (run_f) {
+      out.f.null_step = s0[DS_NULL];
+      out.f.overflow = s0[DS_OVF];
+    }
+    if (run_r) {
+      out.r.null_step = s1[DS_NULL];
+      out.r.overflow = s1[DS_OVF];
+    }
+  }
+  // an overflowing direction ends the search (the host re-runs the pair with wider rows); the other
+  // direction's chunks are not worth computing then
+  if (out.f.overflow || out.r.overflow) return out;
+  const int nch0 = cx.sh->ds[0][DS_NCH];
+  const int nch_all = nch0 + cx.sh->ds[1][DS_NCH];
+  int32_t* ring = df.st.base;
 #if WFA_DEVICE
   asm volatile("" : "+l"(ring));  // keep the ring base as one materialised 64-bit pointer (row address = one IMAD.WIDE)
   __builtin_assume(__isGlobal(ring));
 #endif
-  PROF_T(t2);
-  const int lo_al = lo & ~3;  // arithmetic: rounds towards -inf on two's complement
-  // Chunks are claimed from a shared counter instead of being dealt round-robin: the two fringe
-  // chunks (masked reads, per-cell trims: ~1.5x an interior chunk) go first, then the interior, so
-  // the warps reach the closing barrier of the step together whatever the chunks cost.
-  const int nchunks = (hi - lo_al) / CH + 1;
-  (void)nwarps;
+  const Dir& d = df;  // fields shared by both directions: sequences, lengths, packing
+  const uint32_t tlen = (uint32_t)d.tlen, plen = (uint32_t)d.plen;
+  // trims are accumulated in registers over the chunks a warp takes from one direction and go to
+  // that direction's reduction slots when the warp moves on (lanes 0..10 issue one atomic each)
+  Span4 sp0, sp1, sp2, sp3, sp4;
+  int max_ak = 0, acc_dir = -1;
+  auto flush = [&](int fdir) {
+    max_ak = warp_max(max_ak);
+    {
+      RedSlots* red = &cx.sh->red[fdir];
+#if WFA_DEVICE
+      int v = max_ak;
+      v = lane == 0 ? sp0.mn : lane == 1 ? sp1.mn : lane == 2 ? sp2.mn : lane == 3 ? sp3.mn : lane == 4 ? sp4.mn : v;
+      v = lane == 5 ? sp0.mx : lane == 6 ? sp1.mx : lane == 7 ? sp2.mx : lane == 8 ? sp3.mx : lane == 9 ? sp4.mx : v;
+      int* slot = &red->mn[0] + lane;  // RedSlots = mn[5], mx[5], max_ak: eleven consecutive ints
+      if (lane < 5) {
+        if (v != INT32_MAX) atomicMin(slot, v);
+      } else if (lane < 10) {
+        if (v != INT32_MIN) atomicMax(slot, v);
+      } else if (lane == 10) {
+        if (v > 0) atomicMax(slot, v);
+      }
+#else
+      const int mns[5] = {sp0.mn, sp1.mn, sp2.mn, sp3.mn, sp4.mn};
+      const int mxs[5] = {sp0.mx, sp1.mx, sp2.mx, sp3.mx, sp4.mx};
+      if (max_ak > 0) sh_atomic_max(&red->max_ak, max_ak);
+      for (int c = 0; c < 5; ++c) {
+        if (mns[c] != INT32_MAX) {
+          sh_atomic_min(&red->mn[c], mns[c]);
+          sh_atomic_max(&red->mx[c], mxs[c]);
+        }
+      }
+#endif
+    }
+  };
+  // Chunks of both directions are claimed from one shared counter; inside a direction the two
+  // fringe chunks (masked reads, per-cell trims: ~1.5x an interior chunk) go first.
   while (true) {
     int claim = 0;
 #if WFA_DEVICE
@@ -950,8 +1064,25 @@ WFA_FN StepOut wf_step_vec(Ctx& cx, Dir& d, const Penalties& pen, int s) {
 #else
     claim = cx.sh->chunk_ctr++;
 #endif
-    if (claim >= nchunks) break;
-    const int ci = claim == 0 ? 0 : (claim == 1 ? nchunks - 1 : claim - 1);
+    if (claim >= nch_all) break;
+    const int dir = claim >= nch0 ? 1 : 0;
+    const volatile int* su = cx.sh->ds[dir];
+    const int cl = claim - (dir ? nch0 : 0), nchunks = su[DS_NCH];
+    const int ci = cl == 0 ? 0 : (cl == 1 ? nchunks - 1 : cl - 1);
+    const int lo = su[DS_LO], hi = su[DS_HI], lo_al = su[DS_LOAL];
+    const int fl = su[DS_FLAGS];
+    const bool a_i1 = fl & 1, a_i2 = fl & 2, a_d1 = fl & 4, a_d2 = fl & 8;
+    const int dp0 = su[DS_P0], dt0 = su[DS_T0], drev = su[DS_REV], dcend = su[DS_CEND];
+    if (dir != acc_dir) {
+      if (acc_dir >= 0) flush(acc_dir);
+      sp0.init();
+      sp1.init();
+      sp2.init();
+      sp3.init();
+      sp4.init();
+      max_ak = 0;
+      acc_dir = dir;
+    }
     const int kb = lo_al + ci * CH;
     const int k0 = kb + 4 * lane;
     int32_t ins1[4], ins2[4], del1[4], del2[4], mx[4];
@@ -963,14 +1094,14 @@ WFA_FN StepOut wf_step_vec(Ctx& cx, Dir& d, const Penalties& pen, int s) {
     // the row); kq is a safe stand-in address for them
     const bool lane_act = k0 <= hi;
     const int kq = lane_act ? k0 : lo_al;
-    const int32_t* const r_o1 = ring + (su[SU_O1] + kq);
-    const int32_t* const r_o2 = ring + (su[SU_O2] + kq);
-    const int32_t* const r_i1 = ring + (su[SU_I1] + kq);
-    const int32_t* const r_i2 = ring + (su[SU_I2] + kq);
-    const int32_t* const r_d1 = ring + (su[SU_D1] + kq);
-    const int32_t* const r_d2 = ring + (su[SU_D2] + kq);
+    const int32_t* const r_o1 = ring + (su[DS_O1] + kq);
+    const int32_t* const r_o2 = ring + (su[DS_O2] + kq);
+    const int32_t* const r_i1 = ring + (su[DS_I1] + kq);
+    const int32_t* const r_i2 = ring + (su[DS_I2] + kq);
+    const int32_t* const r_d1 = ring + (su[DS_D1] + kq);
+    const int32_t* const r_d2 = ring + (su[DS_D2] + kq);
     I4 vo1 = ld4(r_o1), vo2 = ld4(r_o2), vi1 = ld4(r_i1), vi2 = ld4(r_i2);
-    I4 vd1 = ld4(r_d1), vd2 = ld4(r_d2), vmis = ld4(ring + (su[SU_MIS] + kq));
+    I4 vd1 = ld4(r_d1), vd2 = ld4(r_d2), vmis = ld4(ring + (su[DS_MIS] + kq));
     // chunk-edge neighbours: issued together with the row reads (before the shuffles wait for
     // those), so a chunk pays one global-memory latency, not two
     int32_t eL0 = 0, eL1 = 0, eL2 = 0, eL3 = 0, eR0 = 0, eR1 = 0, eR2 = 0, eR3 = 0;
@@ -1000,10 +1131,14 @@ WFA_FN StepOut wf_step_vec(Ctx& cx, Dir& d, const Penalties& pen, int s) {
       d1R = eR2;
       d2R = eR3;
     }
-    const bool interior = kb >= su[SU_INLO] && kb + CH - 1 <= su[SU_INHI];  // warp-uniform
+    const bool interior = kb >= su[DS_INLO] && kb + CH - 1 <= su[DS_INHI];  // warp-uniform
     if (!interior) {
       // fringe chunk: whatever lies outside its source wavefront reads as NULL
       // (WFA/wavefront_compute.c:251-295 pads the same way)
+      const WfMeta m_o1 = {su[DS_META + 0], su[DS_META + 1]}, m_o2 = {su[DS_META + 2], su[DS_META + 3]};
+      const WfMeta m_i1 = {su[DS_META + 4], su[DS_META + 5]}, m_i2 = {su[DS_META + 6], su[DS_META + 7]};
+      const WfMeta m_d1 = {su[DS_META + 8], su[DS_META + 9]}, m_d2 = {su[DS_META + 10], su[DS_META + 11]};
+      const WfMeta m_mis = {su[DS_META + 12], su[DS_META + 13]};
 #define MSK(v, m, kk) v = ((kk) >= (m).lo && (kk) <= (m).hi) ? v : OFFSET_NULL
       MSK(o1L, m_o1, k0 - 1);
       MSK(vo1.x, m_o1, k0);
@@ -1070,10 +1205,10 @@ WFA_FN StepOut wf_step_vec(Ctx& cx, Dir& d, const Penalties& pen, int s) {
     // gap components of this score (rows of components that are not allocated this step are never
     // read: their meta says absent)
     if (lane_act) {
-      st4(ring + (su[SU_WI1] + k0), ins1[0], ins1[1], ins1[2], ins1[3]);
-      st4(ring + (su[SU_WI2] + k0), ins2[0], ins2[1], ins2[2], ins2[3]);
-      st4(ring + (su[SU_WD1] + k0), del1[0], del1[1], del1[2], del1[3]);
-      st4(ring + (su[SU_WD2] + k0), del2[0], del2[1], del2[2], del2[3]);
+      st4(ring + (su[DS_WI1] + k0), ins1[0], ins1[1], ins1[2], ins1[3]);
+      st4(ring + (su[DS_WI2] + k0), ins2[0], ins2[1], ins2[2], ins2[3]);
+      st4(ring + (su[DS_WD1] + k0), del1[0], del1[1], del1[2], del1[3]);
+      st4(ring + (su[DS_WD2] + k0), del2[0], del2[1], del2[2], del2[3]);
     }
     if (warp_all(all_ok)) {
       // every cell of the chunk is in bounds in all five components (then all are allocated too)
@@ -1113,35 +1248,35 @@ WFA_FN StepOut wf_step_vec(Ctx& cx, Dir& d, const Penalties& pen, int s) {
       uint32_t xw[4];
       int room[4];
       const int per = 32 >> d.lbits;
-      const int rev = d.reverse, sgn = rev ? -1 : 1;
+      const int rev = drev, sgn = rev ? -1 : 1;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const int h = vm[j] ? mx[j] : 0, v = vm[j] ? mx[j] - (k0 + j) : 0;
         room[j] = imin(d.plen - v, d.tlen - h);
-        xw[j] = pk_window_dir(d.P, d.p0 + sgn * v, d.lbits, rev) ^ pk_window_dir(d.T, d.t0 + sgn * h, d.lbits, rev);
+        xw[j] = pk_window_dir(d.P, dp0 + sgn * v, d.lbits, rev) ^ pk_window_dir(d.T, dt0 + sgn * h, d.lbits, rev);
       }
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         int n = pk_match_len(xw[j], d.lbits, rev);
         if (vm[j] && xw[j] == 0 && per < room[j]) {
           const int h = mx[j] + per, v = mx[j] - (k0 + j) + per;
-          n += lcp_dir(d.P, d.T, d.p0 + sgn * v, d.t0 + sgn * h, room[j] - per, d.lbits, rev);
+          n += lcp_dir(d.P, d.T, dp0 + sgn * v, dt0 + sgn * h, room[j] - per, d.lbits, rev);
         }
         const int32_t e = mx[j] + imin(n, room[j]);
         mx[j] = vm[j] ? e : mx[j];
         max_ak = imax(max_ak, vm[j] ? 2 * e - (k0 + j) : 0);
       }
     }
-    if (lane_act) st4(ring + (su[SU_WM] + k0), mx[0], mx[1], mx[2], mx[3]);
+    if (lane_act) st4(ring + (su[DS_WM] + k0), mx[0], mx[1], mx[2], mx[3]);
     {
       // end cell of this search (WFA/wavefront_termination.c:37-113) for the test in step_finish
       const unsigned je = (unsigned)(d.tlen - d.plen - k0);
       if (je < 4u) {
-        const int ce = d.cend;
+        const int ce = dcend;
 #define SEL4(a) (je == 0 ? a[0] : je == 1 ? a[1] : je == 2 ? a[2] : a[3])
         const int32_t e_m = SEL4(mx), e_i1 = SEL4(ins1), e_i2 = SEL4(ins2), e_d1 = SEL4(del1), e_d2 = SEL4(del2);
 #undef SEL4
-        cx.sh->end_val = ce == C_M ? e_m : ce == C_I1 ? e_i1 : ce == C_I2 ? e_i2 : ce == C_D1 ? e_d1 : e_d2;
+        cx.sh->end_val[dir] = ce == C_M ? e_m : ce == C_I1 ? e_i1 : ce == C_I2 ? e_i2 : ce == C_D1 ? e_d1 : e_d2;
       }
     }
 #ifdef WFA_PROFILE
@@ -1157,41 +1292,68 @@ WFA_FN StepOut wf_step_vec(Ctx& cx, Dir& d, const Penalties& pen, int s) {
     }
 #endif
   }
-  // merge the per-warp trims, publish metas and antidiagonal bounds (as in wf_step)
+  if (acc_dir >= 0) flush(acc_dir);
   PROF_T(t3);
-  StepCtl ctl;
-  ctl.s = s;
-  ctl.slot5 = slot5;
-  ctl.s_o1 = s_o1;
-  ctl.s_e1 = s_e1;
-  ctl.s_o2 = s_o2;
-  ctl.s_e2 = s_e2;
-  ctl.n_o1 = n_o1;
-  ctl.n_o2 = n_o2;
-  ctl.n_i1 = n_i1;
-  ctl.n_d1 = n_d1;
-  ctl.n_i2 = n_i2;
-  ctl.n_d2 = n_d2;
-  ctl.a_i1 = a_i1;
-  ctl.a_i2 = a_i2;
-  ctl.a_d1 = a_d1;
-  ctl.a_d2 = a_d2;
-  const int mns[5] = {sp0.mn, sp1.mn, sp2.mn, sp3.mn, sp4.mn};
-  const int mxs[5] = {sp0.mx, sp1.mx, sp2.mx, sp3.mx, sp4.mx};
-  step_finish(cx, d, ctl, mns, mxs, max_ak, o, true);
+  cta_sync();  // E
+  // F: publish (lanes 0..4 of warp 0 for the forward direction, of warp 1 -- or threads 5..9 of a
+  // one-warp CTA -- for the reverse direction), results for every thread
+  for (int dir = 0; dir < 2; ++dir) {
+    if (!(dir ? run_r : run_f)) continue;
+    StepOut& o = dir ? out.r : out.f;
+    if (o.null_step) continue;
+    const Dir& dd = dir ? dr : df;
+    const volatile int* su = cx.sh->ds[dir];
+    const RedSlots* red = &cx.sh->red[dir];
+    StepCtl t;
+    t.s = su[DS_S];
+    t.slot5 = su[DS_SLOT5];
+    t.s_o1 = su[DS_SO1];
+    t.s_e1 = su[DS_SE1];
+    t.s_o2 = su[DS_SO2];
+    t.s_e2 = su[DS_SE2];
+    const int nf = su[DS_NFLAGS], fl = su[DS_FLAGS];
+    t.n_o1 = nf & 1;
+    t.n_o2 = nf & 2;
+    t.n_i1 = nf & 4;
+    t.n_d1 = nf & 8;
+    t.n_i2 = nf & 16;
+    t.n_d2 = nf & 32;
+    t.a_i1 = fl & 1;
+    t.a_i2 = fl & 2;
+    t.a_d1 = fl & 4;
+    t.a_d2 = fl & 8;
+    o.max_ak = red->max_ak;
+#if WFA_DEVICE
+    const int pub0 = (nwarps > 1 && dir == 1) ? 32 : 5 * dir;
+    if (cx.tid >= pub0 && cx.tid < pub0 + 5) publish_comp(dd.st, red, t, cx.tid - pub0);
+#else
+    for (int c = 0; c < 5; ++c) publish_comp(dd.st, red, t, c);
+#endif
+    if (cx.tid == 0) cx.sh->cells += (unsigned long long)su[DS_WIDTH];
+    // termination (WFA/wavefront_termination.c:37-113) from the reduction slots and the stashed end cell
+    {
+      const int ak = dd.tlen - dd.plen;
+      const int ce = dd.cend;
+      const bool al = ce == C_M ? true : ce == C_I1 ? t.a_i1 : ce == C_I2 ? t.a_i2 : ce == C_D1 ? t.a_d1 : t.a_d2;
+      const bool present = al && red->mn[ce] <= red->mx[ce];
+      if (present && red->mn[ce] <= ak && ak <= red->mx[ce]) {
+        if (cx.sh->end_val[dir] >= dd.tlen) o.end_reached = 1;
+      }
+    }
+  }
 #ifdef WFA_PROFILE
   if (cx.tid == 0) {
     const long long t6 = clock64();
     unsigned long long* pf = cx.sh->prof;
-    pf[0] += 1;
+    pf[0] += (run_f ? 1 : 0) + (run_r ? 1 : 0);
     pf[1] += t1 - t0;  // wait at the top barrier
-    pf[2] += t2 - t1;  // metas, limits, row pointers
+    pf[2] += t2 - t1;  // setup (one warp per direction) + barrier
     pf[3] += t3 - t2;  // chunk loop (warp 0)
-    pf[4] += t6 - t3;  // step_finish: reduce, second barrier, publish, end test
-    pf[7] += (unsigned long long)(hi - lo + 1);
+    pf[4] += t6 - t3;  // closing barrier, publish, end test
+    pf[7] += (unsigned long long)(cx.sh->ds[0][DS_NCH] ? cx.sh->ds[0][DS_WIDTH] : 0) + (cx.sh->ds[1][DS_NCH] ? cx.sh->ds[1][DS_WIDTH] : 0);
   }
 #endif
-  return o;
+  return out;
 }
 
 // reset reduction slots (thread 0) -- call before the first wf_step of a search
@@ -1379,10 +1541,19 @@ WFA_FN int wf_find_breakpoint(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
   long long score_bound = 2ll * imax(pen.o1, pen.o2) + (long long)(df.plen + df.tlen) * imax(pen.e1, pen.e2);
   if (score_hint < score_bound) score_bound = score_hint;
   score_bound += 4ll * pen.scope + 64;
+  // While the searches are far apart both directions advance in one dual step. The reference tests
+  // for closeness between the forward and the reverse step; when that test fires after the forward
+  // half, the reverse half has already run, so its result is parked and the loop replays the
+  // reference order: the reverse turn of the second phase does its overlap search (the ring keeps
+  // scope+1 score slots, so the row of score_r-25 is still intact beside the new row of score_r+1)
+  // and then takes the parked step instead of computing it.
+  bool parked = false;
+  StepOut parked_out = o;
   while (true) {
     if ((long long)score_f + score_r > score_bound) return 3;
     if (!close && fwd_max_ak + rev_max_ak >= max_antidiagonal) close = true;
     const bool tf = turn_forward;
+    const bool dual = !close && tf;
     const int own = tf ? score_f : score_r, oth = tf ? score_r : score_f;
     if (close) {
       const int min_own = (own > scope - 1) ? own - (scope - 1) : 0;
@@ -1392,31 +1563,42 @@ WFA_FN int wf_find_breakpoint(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
       const Dir a = tf ? dr : df, b = tf ? df : dr;
       wf_overlap(cx, a, b, pen, oth, own, !tf);
     }
-    // one copy of the step code for both directions: the moving aligner is selected into d
-    Dir d = tf ? df : dr;
-    o = wf_step_vec(cx, d, pen, own + 1);
-    if (tf) {
-      df.st.cur_s = d.st.cur_s;
-      df.st.cur_slot = d.st.cur_slot;
+    StepOut2 o2;
+    o2.f = o;
+    o2.r = o;
+    const bool run_f = dual || tf, run_r = (dual || !tf) && !parked;
+    if (run_f || run_r) o2 = wf_step_multi(cx, df, dr, pen, score_f + 1, score_r + 1, run_f, run_r);
+    if (run_f) {
       ++score_f;
-    } else {
-      dr.st.cur_s = d.st.cur_s;
-      dr.st.cur_slot = d.st.cur_slot;
-      ++score_r;
-    }
-    if (o.overflow) return 2;
-    if (!close) {
-      if (tf) {
-        if (fwd_max_ak < o.max_ak) fwd_max_ak = o.max_ak;
-      } else {
-        if (rev_max_ak < o.max_ak) rev_max_ak = o.max_ak;
+      if (o2.f.overflow) return 2;
+      if (!close && fwd_max_ak < o2.f.max_ak) fwd_max_ak = o2.f.max_ak;
+      if (o2.f.end_reached) {
+        *score_reached = score_f;
+        return 1;
+      }
+      turn_forward = false;
+      if (dual && fwd_max_ak + rev_max_ak >= max_antidiagonal) {
+        // closeness reached between the two halves: replay the reverse turn in reference order
+        parked = true;
+        parked_out = o2.r;
+        continue;
       }
     }
-    if (o.end_reached) {
-      *score_reached = own + 1;
-      return 1;
+    if (dual || !tf) {
+      StepOut orv = o2.r;
+      if (parked) {
+        orv = parked_out;
+        parked = false;
+      }
+      ++score_r;
+      if (orv.overflow) return 2;
+      if (!close && rev_max_ak < orv.max_ak) rev_max_ak = orv.max_ak;
+      if (orv.end_reached) {
+        *score_reached = score_r;
+        return 1;
+      }
+      turn_forward = true;
     }
-    turn_forward = !tf;
   }
   return 0;
 }
@@ -1658,7 +1840,7 @@ WFA_FN PairResult wf_align_pair(Ctx& cx, const SeqView& sv, int plen, int tlen, 
   df.st.meta = sh->meta_f;
   df.st.ub = sh->ub_f;
   df.st.modular = 1;
-  df.st.scope = pen.scope;
+  df.st.scope = pen.scope + 1;  // ring slots: one more than the reference's scope (see the dual step)
   df.st.W = ws.W;
   df.st.cap = 0;
   df.st.cur_s = INT32_MIN / 2;

@@ -45,7 +45,7 @@ extern "C" int emul_wfa_align(const char* pattern, int plen, const char* text, i
   if (lbits <= 0 || lbits < pk.min_lbits()) lbits = pk.min_lbits();
   std::vector<uint32_t> pb = pk.pack(pattern, plen, lbits), tb = pk.pack(text, tlen, lbits);
   SeqView sv{pb.data() + 4, tb.data() + 4, lbits};
-  std::vector<int32_t> rf((size_t)pen.scope * 5 * W), rr((size_t)pen.scope * 5 * W), full((size_t)5 * cap * cap);
+  std::vector<int32_t> rf((size_t)(pen.scope + 1) * 5 * W), rr((size_t)(pen.scope + 1) * 5 * W), full((size_t)5 * cap * cap);
   std::vector<WfMeta> fm((size_t)cap * 5);
   PairWorkspace ws{rf.data(), rr.data(), W, full.data(), fm.data(), cap};
   std::vector<uint32_t> runs(plen + tlen + 8), bt(plen + tlen + 8);
