@@ -988,8 +988,14 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
   cta_sync();  // A
   PROF_T(t1);
   // B
-  if (run_f && warp == 0) wf_setup_dir(cx, df, pen, sf, 0, 0, lane);
-  if (run_r && warp == (1 % nwarps)) wf_setup_dir(cx, dr, pen, sr, 1, (int)(dr.st.base - df.st.base), lane);
+  // (one copy of the setup code: the direction is selected at run time, the hot code of a dual step
+  // has to stay inside the 32 KB instruction cache)
+#pragma unroll 1
+  for (int dir = 0; dir < 2; ++dir) {
+    if (!(dir ? run_r : run_f) || warp != (dir % nwarps)) continue;
+    const Dir dd = dir ? dr : df;
+    wf_setup_dir(cx, dd, pen, dir ? sr : sf, dir, dir ? (int)(dr.st.base - df.st.base) : 0, lane);
+  }
   if (cx.tid == 0) {
     cx.sh->chunk_ctr = 0;
     if (!run_f) cx.sh->ds[0][DS_NCH] = 0;
@@ -1064,17 +1070,11 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
 #else
     claim = cx.sh->chunk_ctr++;
 #endif
-    if (claim >= nch_all) break;
-    const int dir = claim >= nch0 ? 1 : 0;
-    const volatile int* su = cx.sh->ds[dir];
-    const int cl = claim - (dir ? nch0 : 0), nchunks = su[DS_NCH];
-    const int ci = cl == 0 ? 0 : (cl == 1 ? nchunks - 1 : cl - 1);
-    const int lo = su[DS_LO], hi = su[DS_HI], lo_al = su[DS_LOAL];
-    const int fl = su[DS_FLAGS];
-    const bool a_i1 = fl & 1, a_i2 = fl & 2, a_d1 = fl & 4, a_d2 = fl & 8;
-    const int dp0 = su[DS_P0], dt0 = su[DS_T0], drev = su[DS_REV], dcend = su[DS_CEND];
+    const bool done = claim >= nch_all;
+    const int dir = done ? -1 : (claim >= nch0 ? 1 : 0);
     if (dir != acc_dir) {
-      if (acc_dir >= 0) flush(acc_dir);
+      if (acc_dir >= 0) flush(acc_dir);  // the only flush site: a direction change or the end of the pool
+      if (done) break;
       sp0.init();
       sp1.init();
       sp2.init();
@@ -1083,6 +1083,14 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
       max_ak = 0;
       acc_dir = dir;
     }
+    if (done) break;  // a warp that claimed nothing has acc_dir == dir == -1
+    const volatile int* su = cx.sh->ds[dir];
+    const int cl = claim - (dir ? nch0 : 0), nchunks = su[DS_NCH];
+    const int ci = cl == 0 ? 0 : (cl == 1 ? nchunks - 1 : cl - 1);
+    const int lo = su[DS_LO], hi = su[DS_HI], lo_al = su[DS_LOAL];
+    const int fl = su[DS_FLAGS];
+    const bool a_i1 = fl & 1, a_i2 = fl & 2, a_d1 = fl & 4, a_d2 = fl & 8;
+    const int dp0 = su[DS_P0], dt0 = su[DS_T0], drev = su[DS_REV], dcend = su[DS_CEND];
     const int kb = lo_al + ci * CH;
     const int k0 = kb + 4 * lane;
     int32_t ins1[4], ins2[4], del1[4], del2[4], mx[4];
@@ -1255,13 +1263,30 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
         room[j] = imin(d.plen - v, d.tlen - h);
         xw[j] = pk_window_dir(d.P, dp0 + sgn * v, d.lbits, rev) ^ pk_window_dir(d.T, dt0 + sgn * h, d.lbits, rev);
       }
+      int nn[4];
+      unsigned need = 0;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        int n = pk_match_len(xw[j], d.lbits, rev);
-        if (vm[j] && xw[j] == 0 && per < room[j]) {
-          const int h = mx[j] + per, v = mx[j] - (k0 + j) + per;
-          n += lcp_dir(d.P, d.T, dp0 + sgn * v, dt0 + sgn * h, room[j] - per, d.lbits, rev);
-        }
+        nn[j] = pk_match_len(xw[j], d.lbits, rev);
+        if (vm[j] && xw[j] == 0 && per < room[j]) need |= 1u << j;
+      }
+      // rare: a cell whose whole first window matched walks on (one copy of the walk for the four cells)
+#pragma unroll 1
+      while (need) {
+        const int j = ctz32z(need);
+        need &= need - 1;
+        const int mxj = j == 0 ? mx[0] : j == 1 ? mx[1] : j == 2 ? mx[2] : mx[3];
+        const int rj = j == 0 ? room[0] : j == 1 ? room[1] : j == 2 ? room[2] : room[3];
+        const int h = mxj + per, v = mxj - (k0 + j) + per;
+        const int extra = lcp_dir(d.P, d.T, dp0 + sgn * v, dt0 + sgn * h, rj - per, d.lbits, rev);
+        nn[0] += j == 0 ? extra : 0;
+        nn[1] += j == 1 ? extra : 0;
+        nn[2] += j == 2 ? extra : 0;
+        nn[3] += j == 3 ? extra : 0;
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int n = nn[j];
         const int32_t e = mx[j] + imin(n, room[j]);
         mx[j] = vm[j] ? e : mx[j];
         max_ak = imax(max_ak, vm[j] ? 2 * e - (k0 + j) : 0);
@@ -1292,16 +1317,16 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
     }
 #endif
   }
-  if (acc_dir >= 0) flush(acc_dir);
   PROF_T(t3);
   cta_sync();  // E
   // F: publish (lanes 0..4 of warp 0 for the forward direction, of warp 1 -- or threads 5..9 of a
   // one-warp CTA -- for the reverse direction), results for every thread
+#pragma unroll 1
   for (int dir = 0; dir < 2; ++dir) {
     if (!(dir ? run_r : run_f)) continue;
-    StepOut& o = dir ? out.r : out.f;
+    StepOut o = dir ? out.r : out.f;
     if (o.null_step) continue;
-    const Dir& dd = dir ? dr : df;
+    const Dir dd = dir ? dr : df;
     const volatile int* su = cx.sh->ds[dir];
     const RedSlots* red = &cx.sh->red[dir];
     StepCtl t;
@@ -1340,6 +1365,8 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
         if (cx.sh->end_val[dir] >= dd.tlen) o.end_reached = 1;
       }
     }
+    if (dir) out.r = o;
+    else out.f = o;
   }
 #ifdef WFA_PROFILE
   if (cx.tid == 0) {
