@@ -802,34 +802,25 @@ WFA_FN void st4(int32_t* p, int32_t a, int32_t b, int32_t c, int32_t e) {
 }
 
 // first/last valid diagonal of one component inside a chunk where lane l holds diagonals kb+4l+j
-struct Span4 {
+struct Span4 {  // LANE-local first/last valid diagonal of one component; reduced over the warp when flushed
   int mn, mx;
   WFA_FN void init() {
     mn = INT32_MAX;
     mx = INT32_MIN;
   }
-  WFA_FN void add_full(int kb, int n) {
-    mn = imin(mn, kb);
-    mx = imax(mx, kb + n - 1);
+  WFA_FN void add_full(int k0) {
+    mn = imin(mn, k0);
+    mx = imax(mx, k0 + 3);
   }
-  WFA_FN void add(bool p0, bool p1, bool p2, bool p3, int kb) {
-    const uint32_t b0 = warp_ballot(p0), b1 = warp_ballot(p1), b2 = warp_ballot(p2), b3 = warp_ballot(p3);
-    if (b0) {
-      mn = imin(mn, kb + 4 * ctz32(b0));
-      mx = imax(mx, kb + 4 * (31 - clz32(b0)));
-    }
-    if (b1) {
-      mn = imin(mn, kb + 4 * ctz32(b1) + 1);
-      mx = imax(mx, kb + 4 * (31 - clz32(b1)) + 1);
-    }
-    if (b2) {
-      mn = imin(mn, kb + 4 * ctz32(b2) + 2);
-      mx = imax(mx, kb + 4 * (31 - clz32(b2)) + 2);
-    }
-    if (b3) {
-      mn = imin(mn, kb + 4 * ctz32(b3) + 3);
-      mx = imax(mx, kb + 4 * (31 - clz32(b3)) + 3);
-    }
+  WFA_FN void add(bool p0, bool p1, bool p2, bool p3, int k0) {
+    const int f = p0 ? k0 : p1 ? k0 + 1 : p2 ? k0 + 2 : p3 ? k0 + 3 : INT32_MAX;
+    const int l = p3 ? k0 + 3 : p2 ? k0 + 2 : p1 ? k0 + 1 : p0 ? k0 : INT32_MIN;
+    mn = imin(mn, f);
+    mx = imax(mx, l);
+  }
+  WFA_FN void reduce() {
+    mn = warp_min(mn);
+    mx = warp_max(mx);
   }
 };
 
@@ -1033,6 +1024,11 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
   int max_ak = 0, acc_dir = -1;
   auto flush = [&](int fdir) {
     max_ak = warp_max(max_ak);
+    sp0.reduce();
+    sp1.reduce();
+    sp2.reduce();
+    sp3.reduce();
+    sp4.reduce();
     {
       RedSlots* red = &cx.sh->red[fdir];
 #if WFA_DEVICE
@@ -1220,11 +1216,11 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
     }
     if (warp_all(all_ok)) {
       // every cell of the chunk is in bounds in all five components (then all are allocated too)
-      sp0.add_full(kb, CH);
-      sp1.add_full(kb, CH);
-      sp2.add_full(kb, CH);
-      sp3.add_full(kb, CH);
-      sp4.add_full(kb, CH);
+      sp0.add_full(k0);
+      sp1.add_full(k0);
+      sp2.add_full(k0);
+      sp3.add_full(k0);
+      sp4.add_full(k0);
     } else {
       bool a0 = true, a1 = true, a2 = true, a3 = true;
       if (!interior) {
@@ -1233,19 +1229,19 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
         a2 = k0 + 2 >= lo && k0 + 2 <= hi;
         a3 = k0 + 3 >= lo && k0 + 3 <= hi;
       }
-      sp0.add(vm[0], vm[1], vm[2], vm[3], kb);
+      sp0.add(vm[0], vm[1], vm[2], vm[3], k0);
       if (a_i1)
         sp1.add(a0 && in_bounds(ins1[0], k0, tlen, plen), a1 && in_bounds(ins1[1], k0 + 1, tlen, plen),
-                a2 && in_bounds(ins1[2], k0 + 2, tlen, plen), a3 && in_bounds(ins1[3], k0 + 3, tlen, plen), kb);
+                a2 && in_bounds(ins1[2], k0 + 2, tlen, plen), a3 && in_bounds(ins1[3], k0 + 3, tlen, plen), k0);
       if (a_i2)
         sp2.add(a0 && in_bounds(ins2[0], k0, tlen, plen), a1 && in_bounds(ins2[1], k0 + 1, tlen, plen),
-                a2 && in_bounds(ins2[2], k0 + 2, tlen, plen), a3 && in_bounds(ins2[3], k0 + 3, tlen, plen), kb);
+                a2 && in_bounds(ins2[2], k0 + 2, tlen, plen), a3 && in_bounds(ins2[3], k0 + 3, tlen, plen), k0);
       if (a_d1)
         sp3.add(a0 && in_bounds(del1[0], k0, tlen, plen), a1 && in_bounds(del1[1], k0 + 1, tlen, plen),
-                a2 && in_bounds(del1[2], k0 + 2, tlen, plen), a3 && in_bounds(del1[3], k0 + 3, tlen, plen), kb);
+                a2 && in_bounds(del1[2], k0 + 2, tlen, plen), a3 && in_bounds(del1[3], k0 + 3, tlen, plen), k0);
       if (a_d2)
         sp4.add(a0 && in_bounds(del2[0], k0, tlen, plen), a1 && in_bounds(del2[1], k0 + 1, tlen, plen),
-                a2 && in_bounds(del2[2], k0 + 2, tlen, plen), a3 && in_bounds(del2[3], k0 + 3, tlen, plen), kb);
+                a2 && in_bounds(del2[2], k0 + 2, tlen, plen), a3 && in_bounds(del2[3], k0 + 3, tlen, plen), k0);
     }
     PROF_T(tc1);
     // exact-match extension of the four M cells. The first packed window of all four is compared
