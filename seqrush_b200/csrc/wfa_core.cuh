@@ -1029,31 +1029,29 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
     sp2.reduce();
     sp3.reduce();
     sp4.reduce();
-    {
+    if (lane == 0) {  // shared-memory atomics do not return a value: one lane issues all eleven back to back
       RedSlots* red = &cx.sh->red[fdir];
-#if WFA_DEVICE
-      int v = max_ak;
-      v = lane == 0 ? sp0.mn : lane == 1 ? sp1.mn : lane == 2 ? sp2.mn : lane == 3 ? sp3.mn : lane == 4 ? sp4.mn : v;
-      v = lane == 5 ? sp0.mx : lane == 6 ? sp1.mx : lane == 7 ? sp2.mx : lane == 8 ? sp3.mx : lane == 9 ? sp4.mx : v;
-      int* slot = &red->mn[0] + lane;  // RedSlots = mn[5], mx[5], max_ak: eleven consecutive ints
-      if (lane < 5) {
-        if (v != INT32_MAX) atomicMin(slot, v);
-      } else if (lane < 10) {
-        if (v != INT32_MIN) atomicMax(slot, v);
-      } else if (lane == 10) {
-        if (v > 0) atomicMax(slot, v);
-      }
-#else
-      const int mns[5] = {sp0.mn, sp1.mn, sp2.mn, sp3.mn, sp4.mn};
-      const int mxs[5] = {sp0.mx, sp1.mx, sp2.mx, sp3.mx, sp4.mx};
       if (max_ak > 0) sh_atomic_max(&red->max_ak, max_ak);
-      for (int c = 0; c < 5; ++c) {
-        if (mns[c] != INT32_MAX) {
-          sh_atomic_min(&red->mn[c], mns[c]);
-          sh_atomic_max(&red->mx[c], mxs[c]);
-        }
+      if (sp0.mn != INT32_MAX) {
+        sh_atomic_min(&red->mn[0], sp0.mn);
+        sh_atomic_max(&red->mx[0], sp0.mx);
       }
-#endif
+      if (sp1.mn != INT32_MAX) {
+        sh_atomic_min(&red->mn[1], sp1.mn);
+        sh_atomic_max(&red->mx[1], sp1.mx);
+      }
+      if (sp2.mn != INT32_MAX) {
+        sh_atomic_min(&red->mn[2], sp2.mn);
+        sh_atomic_max(&red->mx[2], sp2.mx);
+      }
+      if (sp3.mn != INT32_MAX) {
+        sh_atomic_min(&red->mn[3], sp3.mn);
+        sh_atomic_max(&red->mx[3], sp3.mx);
+      }
+      if (sp4.mn != INT32_MAX) {
+        sh_atomic_min(&red->mn[4], sp4.mn);
+        sh_atomic_max(&red->mx[4], sp4.mx);
+      }
     }
   };
   // Chunks of both directions are claimed from one shared counter; inside a direction the two
