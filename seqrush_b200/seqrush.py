@@ -29,6 +29,8 @@ class Args:  # the subset of src/seqrush.rs:17-152 that reaches the hot path
     sparsification: str = "none"
     threads: int = 1                    # kept for interface parity; the device schedules pairs itself
     verbose: bool = False
+    output_alignments: Optional[str] = None  # --output-alignments, :693-716
+    paf: Optional[str] = None                # --paf, :463-466
 
 
 def load_sequences(path: str) -> List[Sequence]:
@@ -52,6 +54,26 @@ def load_sequences(path: str) -> List[Sequence]:
         data = b"".join(cur)
         seqs.append(Sequence(cur_id, data, off))
     return seqs
+
+
+def parse_paf_line(line: str):
+    """One PAF record as src/seqrush.rs:529-560 reads it: returns (query_name, query_start, query_end,
+    strand, target_name, target_start, target_end, cigar) or None for an empty line or one with fewer
+    than 12 fields (the reference warns and skips). A record without a cg:Z: tag yields cigar ""
+    (:552-555). Non-numeric coordinates raise ValueError where the reference's unwrap() panics."""
+    line = line.rstrip("\r\n")
+    if not line:
+        return None
+    f = line.split("\t")
+    if len(f) < 12:
+        return None
+    int(f[1]), int(f[6])  # parsed and dropped by the reference too (_query_len, _target_len)
+    cigar = ""
+    for tag in f[12:]:
+        if tag.startswith("cg:Z:"):
+            cigar = tag[5:]
+            break
+    return f[0], int(f[2]), int(f[3]), f[4], f[5], int(f[7]), int(f[8]), cigar
 
 
 class SeqRush:
@@ -84,8 +106,12 @@ class SeqRush:
 
     def align_and_unite(self, args: Args = None, pairs=None, want_results=False):  # :460-508 -> :611-757
         args = args or Args()
+        if args.paf:  # :463-466: a PAF file replaces the alignment phase
+            return self.align_and_unite_from_paf(args.paf, args)
         if args.aligner != "allwave":
             raise SystemExit("only --aligner allwave is implemented on the device")  # :504 exits(1)
+        if args.output_alignments:
+            return self._align_write_paf_and_unite(args, pairs)
         if pairs is None:
             if args.sparsification not in ("none", "None", None):
                 raise NotImplementedError("sparsified pair lists must be passed explicitly (pairs=...)")
@@ -112,6 +138,46 @@ class SeqRush:
         _lib.check(_lib.lib().srgpu_process_alignment(self.ctx._h, self.union_find._h, cigar.encode(), seq1_idx,
                                                       seq2_idx, min_match_len, int(bool(query_is_rc)), query_start,
                                                       target_start))
+
+    def align_and_unite_from_paf(self, paf_path: str, args: Args = None) -> int:  # :510-609
+        """Unite from the alignments of a PAF file (ids looked up by name, unknown names and short lines
+        skipped with a warning, strand "-" = query reverse-complemented); every CIGAR is walked on the
+        device by srgpu_process_alignment. Returns the number of alignments processed."""
+        import sys
+        args = args or Args()
+        idx = {s.id: i for i, s in enumerate(self.sequences)}
+        n = 0
+        with open(paf_path, "r") as f:
+            for line in f:
+                rec = parse_paf_line(line)
+                if rec is None:
+                    if line.strip():
+                        print("Warning: Invalid PAF line (not enough fields): %s" % line.rstrip(), file=sys.stderr)
+                    continue
+                qn, qs, _qe, strand, tn, ts, _te, cigar = rec
+                if qn not in idx or tn not in idx:
+                    print("Warning: Unknown sequence name(s) in PAF: %s or %s" % (qn, tn), file=sys.stderr)
+                    continue
+                self.process_alignment(cigar, idx[qn], idx[tn], args.min_match_length, strand == "-", qs, ts)
+                n += 1
+        return n
+
+    def _align_write_paf_and_unite(self, args: Args, pairs=None, batch: int = 1024):
+        """--output-alignments (:676-716). The reference aligns every pair twice (once for the PAF, once
+        for the graph); here ONE pass over the pair list yields the CIGARs, which go to the file and
+        through the device CIGAR walk. Records are written in pair order."""
+        from .allwave import AllPairIterator, Sequence as AwSequence, alignment_to_paf, cigar_bytes_to_string
+        aw = [AwSequence(s.id, s.data) for s in self.sequences]
+        it = AllPairIterator.with_options(aw, parse_scores(args.scores), False, False, None,
+                                          pairs=self.all_pairs() if pairs is None else pairs, ctx=self.ctx)
+        it._uploaded = True  # the context already holds these sequences (SeqRush.__init__)
+        with open(args.output_alignments, "w") as f:
+            for rs in it._batches(True, batch):
+                for r in rs:
+                    f.write(alignment_to_paf(r, aw) + "\n")
+                    self.process_alignment(cigar_bytes_to_string(r.cigar_bytes), r.query_idx, r.target_idx,
+                                           args.min_match_length, r.is_reverse, 0, 0)
+        return self.ctx.stats()
 
     def count_components(self) -> int:  # :341-353
         return self.union_find.count_components(self.total_length)

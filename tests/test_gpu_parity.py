@@ -283,3 +283,28 @@ def test_forest_merge_on_device(s):
     t = a.union_find.as_tensor()
     assert t.is_cuda and t.numel() == a.union_find.capacity
     ctx.close()
+
+
+def test_paf_out_and_back_in(s, tmp_path):
+    """--output-alignments then --paf (src/seqrush.rs:676-716, :510-609): the partition from the fused
+    path, from the pass that also writes the PAF, and from reading that PAF back are the same."""
+    from seqrush_b200 import synth
+    ids, seqs = synth.make_sequences(6, 3000, 0.02, 21, 0.4, 0.0)
+    mk = lambda ctx: s.SeqRush([s.Sequence(i, a.tobytes()) for i, a in zip(ids, seqs)], ctx=ctx)
+    paf = str(tmp_path / "out.paf")
+    for k in (0, 8):
+        ctx = s.Context(0)
+        a, b, c = mk(ctx), mk(ctx), mk(ctx)  # the context holds one sequence set; these three are the same set
+        a.align_and_unite(s.Args(min_match_length=k))
+        b.align_and_unite(s.Args(min_match_length=k, output_alignments=paf))
+        lines = open(paf).read().splitlines()
+        assert len(lines) == len(ids) ** 2
+        f = lines[1].split("\t")
+        assert len(f) == 13 and f[0] == ids[0] and f[5] == ids[1] and f[12].startswith("cg:Z:") and f[4] in "+-"
+        assert any(l.split("\t")[4] == "-" for l in lines)
+        with open(paf, "a") as fh:  # lines the reference skips: empty, short, unknown name
+            fh.write("\n" + "x\t1\t0\n" + lines[1].replace(ids[0], "nobody") + "\n")
+        assert c.align_and_unite(s.Args(min_match_length=k, paf=paf)) == len(ids) ** 2
+        pa = a.canonical_partition()
+        assert np.array_equal(pa, b.canonical_partition()) and np.array_equal(pa, c.canonical_partition())
+        ctx.close()

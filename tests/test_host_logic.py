@@ -84,3 +84,15 @@ def test_bench_reference_arm_prints_one_json_line():
     d = json.loads(lines[0])
     assert d["impl"] == "reference" and d["cpu_baseline"]["kind"] == "reference" and d["value"] > 0
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["unit"] == "Mbp/s"
+
+
+def test_parse_paf_line():
+    """src/seqrush.rs:529-560: short lines skipped, cg:Z: looked up among the optional fields only."""
+    from seqrush_b200.seqrush import parse_paf_line
+    line = "q\t25\t2\t22\t-\tt\t30\t3\t23\t18\t20\t60\ttp:A:P\tcg:Z:10=1X9=\n"
+    assert parse_paf_line(line) == ("q", 2, 22, "-", "t", 3, 23, "10=1X9=")
+    assert parse_paf_line("\n") is None
+    assert parse_paf_line("q\t25\t0\t25\t+\tt\t30\t0\t25\t25\t25\n") is None  # 11 fields
+    assert parse_paf_line("q\t25\t0\t25\t+\tt\t30\t0\t25\t25\t25\t60\n")[-1] == ""  # no CIGAR tag
+    with pytest.raises(ValueError):
+        parse_paf_line("q\tx\t0\t25\t+\tt\t30\t0\t25\t25\t25\t60\n")
