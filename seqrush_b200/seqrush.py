@@ -179,6 +179,52 @@ class SeqRush:
                                            args.min_match_length, r.is_reverse, 0, 0)
         return self.ctx.stats()
 
+    STABILITY_THRESHOLD = 10  # :1038
+    CHECK_INTERVAL = 10       # :1039
+
+    @staticmethod
+    def _expand_pair(i: int, j: int):
+        """One (i, j) of the iterative mode is a two-sequence AllPairIterator with self pairs
+        (:976-991): (i,i), (i,j), (j,i), (j,j) in that order."""
+        return [(i, i), (i, j), (j, i), (j, j)]
+
+    def align_and_unite_iterative(self, args: Args = None, tree_pairs=(), random_pairs=()):  # :868-1132
+        """--iterative with explicit pair lists (the reference derives them from MinHash sketches and
+        Rust's DefaultHasher, allwave/src/knn_graph.rs — not reproducible here). Phase 1
+        runs every tree pair in one launch; phase 2 runs the random pairs CHECK_INTERVAL at a time and
+        counts components on the device after each group, stopping after STABILITY_THRESHOLD unchanged
+        counts in a row — the reference's check points, so the same prefix of random_pairs is processed
+        and the partition is the reference's. Returns a dict with the counts and pairs processed."""
+        args = args or Args()
+        if args.output_alignments:
+            raise NotImplementedError("--iterative with --output-alignments: write the PAF with align_and_unite")
+        tree_pairs = [(int(i), int(j)) for i, j in tree_pairs]
+        random_pairs = [(int(i), int(j)) for i, j in random_pairs]
+        sub = Args(scores=args.scores, min_match_length=args.min_match_length)
+        if tree_pairs:
+            self.align_and_unite(sub, pairs=[q for p in tree_pairs for q in self._expand_pair(*p)])
+        post_tree = self.count_components()
+        prev, stable, done, stabilized = post_tree, 0, 0, False
+        ci = self.CHECK_INTERVAL
+        for b0 in range(0, len(random_pairs), ci):
+            grp = random_pairs[b0:b0 + ci]
+            self.align_and_unite(sub, pairs=[q for p in grp for q in self._expand_pair(*p)])
+            done += len(grp)
+            if len(grp) < ci:  # the tail shorter than CHECK_INTERVAL is processed without a check (:1089)
+                break
+            cnt = self.count_components()
+            if cnt == prev:
+                stable += 1
+                if stable >= self.STABILITY_THRESHOLD:
+                    stabilized = True
+                    break
+            else:
+                stable = 0
+            prev = cnt
+        return {"post_tree_components": post_tree, "final_components": self.count_components(),
+                "random_pairs_processed": done, "random_pairs_skipped": len(random_pairs) - done,
+                "stabilized": stabilized}
+
     def count_components(self) -> int:  # :341-353
         return self.union_find.count_components(self.total_length)
 

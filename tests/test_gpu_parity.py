@@ -308,3 +308,45 @@ def test_paf_out_and_back_in(s, tmp_path):
         pa = a.canonical_partition()
         assert np.array_equal(pa, b.canonical_partition()) and np.array_equal(pa, c.canonical_partition())
         ctx.close()
+
+
+def test_iterative_early_stop(s, oracle):
+    """--iterative (src/seqrush.rs:868-1132) with explicit pair lists: the grouped device driver stops at
+    the same random pair as the reference's pair-by-pair loop (restated over the oracle) and ends with
+    the same partition."""
+    import _oracle
+    from seqrush_b200 import synth
+    ids, seqs = synth.make_sequences(8, 2000, 0.02, 31, 0.25, 0.0)
+    n = len(ids)
+    tree = [(i, i + 1) for i in range(n - 1)]
+    rng = np.random.default_rng(5)
+    rand = [(int(a), int(b)) for a, b in rng.integers(0, n, size=(400, 2)) if a != b]
+    ctx = s.Context(0)
+    sr = s.SeqRush([s.Sequence(i, a.tobytes()) for i, a in zip(ids, seqs)], ctx=ctx)
+    out = sr.align_and_unite_iterative(s.Args(), tree, rand)
+    # the reference's loop: one pair at a time, check every 10 pairs, stop after 10 unchanged counts
+    ouf = _oracle.OracleUF(sr.total_length)
+    ouf.unite_fr_all(sr.total_length)
+    four = lambda i, j: np.array([(i, i), (i, j), (j, i), (j, j)], dtype=np.uint32)
+    for i, j in tree:
+        oracle.run_pairs(seqs, four(i, j), threads=4, uf=ouf, want_results=False)
+    post_tree = ouf.count_components(sr.total_length)
+    prev, stable, done = post_tree, 0, 0
+    for k, (i, j) in enumerate(rand):
+        oracle.run_pairs(seqs, four(i, j), threads=4, uf=ouf, want_results=False)
+        done = k + 1
+        if (k + 1) % 10 == 0:
+            cnt = ouf.count_components(sr.total_length)
+            if cnt == prev:
+                stable += 1
+                if stable >= 10:
+                    break
+            else:
+                stable = 0
+            prev = cnt
+    assert out["post_tree_components"] == post_tree
+    assert out["random_pairs_processed"] == done and out["stabilized"] == (done < len(rand))
+    assert 100 <= done < len(rand)  # the case does stop early
+    assert out["final_components"] == ouf.count_components(sr.total_length)
+    assert np.array_equal(sr.canonical_partition(), ouf.canonical(2 * sr.total_length))
+    ctx.close()
