@@ -41,6 +41,9 @@ def test_paf_line():
     f = s.alignment_to_paf(r, seqs).split("\t")
     assert f[:9] == ["q", "8", "0", "8", "+", "t", "8", "0", "8"] and f[9:12] == ["7", "8", "60"]
     assert f[12] == "cg:Z:4=1X3="
+    from seqrush_b200.seqrush import parse_paf_line
+    r.is_reverse = True  # what the writer emits is what the --paf reader takes back (src/seqrush.rs:529-560)
+    assert parse_paf_line(s.alignment_to_paf(r, seqs) + "\n") == ("q", 0, 8, "-", "t", 0, 8, "4=1X3=")
 
 
 def test_load_sequences(tmp_path):
