@@ -91,6 +91,11 @@ typedef struct {
   float union_ms;          /* CUDA-event time of the union kernel launches */
   float total_ms;
   float orient_ms;         /* CUDA-event time of the strand-choice (orient) kernel launches */
+  uint32_t failed_pairs;   /* pairs the reference would fail too (WF_STATUS_END_UNREACHABLE -> empty CIGAR, score
+                              i32::MAX, allwave/src/alignment.rs:40-55); they are skipped by the union step. Pairs
+                              that exceed a workspace limit of THIS library never end up here: the call fails with
+                              SRGPU_E_INTERNAL instead of returning a partition that silently lacks them */
+  uint32_t reserved0;
 } srgpu_stats;
 
 const char* srgpu_last_error(void);

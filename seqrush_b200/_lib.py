@@ -68,7 +68,8 @@ class Stats(C.Structure):
                 ("orient_cells", C.c_uint64), ("unite_ops", C.c_uint64), ("unite_links", C.c_uint64),
                 ("runs", C.c_uint64), ("kernel_launches", C.c_uint32), ("align_launches", C.c_uint32),
                 ("union_launches", C.c_uint32), ("retries", C.c_uint32), ("align_ms", C.c_float),
-                ("union_ms", C.c_float), ("total_ms", C.c_float), ("orient_ms", C.c_float)]
+                ("union_ms", C.c_float), ("total_ms", C.c_float), ("orient_ms", C.c_float),
+                ("failed_pairs", C.c_uint32), ("reserved0", C.c_uint32)]
 
 
 class Region(C.Structure):

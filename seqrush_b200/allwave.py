@@ -80,12 +80,17 @@ def cigar_bytes_to_string(cigar_bytes: bytes) -> str:  # allwave/src/alignment.r
     return "".join("%d%s" % (e - s, m.get(int(a[s]), "?")) for s, e in zip(starts, ends))
 
 
-def alignment_to_paf(r: AlignmentResult, seqs: List[Sequence]) -> str:  # allwave/src/lib.rs:71-112
+def alignment_to_paf(r: AlignmentResult, seqs: List[Sequence]) -> str:
+    """allwave/src/lib.rs:71-112, field for field: the 12 mandatory PAF columns with
+    block_len = max(query_end - query_start, target_end - target_start) (:77-79), mapping quality 60,
+    then ``gi:f:{identity:.6}`` (identity = num_matches / alignment_length, 0.0 for an empty
+    alignment, :82-86) and ``cg:Z:`` + cigar_bytes_to_string (:89, :95-111)."""
     q, t = seqs[r.query_idx], seqs[r.target_idx]
-    block = r.alignment_length
-    return "\t".join(str(x) for x in (
+    block_len = max(r.target_end - r.target_start, r.query_end - r.query_start)
+    identity = (r.num_matches / r.alignment_length) if r.alignment_length > 0 else 0.0
+    return "%s\t%d\t%d\t%d\t%s\t%s\t%d\t%d\t%d\t%d\t%d\t%d\tgi:f:%.6f\tcg:Z:%s" % (
         q.id, len(q.seq), r.query_start, r.query_end, "-" if r.is_reverse else "+", t.id, len(t.seq),
-        r.target_start, r.target_end, r.num_matches, block, 60, "cg:Z:" + cigar_bytes_to_string(r.cigar_bytes)))
+        r.target_start, r.target_end, r.num_matches, block_len, 60, identity, cigar_bytes_to_string(r.cigar_bytes))
 
 
 class AllPairIterator:

@@ -153,6 +153,7 @@ extern "C" int srgpu_ctx_create(int device, void* stream, srgpu_ctx** out) {
     c->own_stream = true;
   }
   for (int i = 0; i < 6; ++i) CK(cudaEventCreate(&c->ev[i]));
+  if (const char* e = getenv("SRGPU_SMEM_BUDGET")) c->smem_budget = atoi(e);  // tuning: 0 = never stage sequences
   *out = c;
   return SRGPU_OK;
 }
@@ -186,8 +187,8 @@ extern "C" int srgpu_ctx_configure(srgpu_ctx* c, int threads, int ctas_per_sm, i
   if (!c) return SRGPU_E_ARG;
   std::lock_guard<std::mutex> lk(c->mu);
   if (threads) {
-    if (threads != 64 && threads != 128 && threads != 256 && threads != 512) {
-      g_err = "threads must be 64, 128, 256 or 512";
+    if (threads != 32 && threads != 64 && threads != 128 && threads != 256 && threads != 512) {
+      g_err = "threads must be 32, 64, 128, 256 or 512";
       return SRGPU_E_ARG;
     }
     c->threads = threads;
@@ -362,20 +363,20 @@ static int check_penalties(const srgpu_penalties* p, Penalties* out) {
   return 0;
 }
 
+// (the dynamic shared-memory attribute is per device and per function: it is set on every launch --
+// a host-side call of a few hundred nanoseconds -- instead of being remembered in a process-wide
+// static, which was wrong for a second context on another GPU of the same process)
 template <int T, int C>
 static cudaError_t launch_align_tc(const AlignArgs& a, int grid, size_t smem, cudaStream_t s) {
-  static size_t configured = 0;
-  if (smem > configured) {
-    cudaError_t e = cudaFuncSetAttribute(align_kernel<T, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    configured = smem;
-  }
+  cudaError_t e = cudaFuncSetAttribute(align_kernel<T, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
   align_kernel<T, C><<<grid, T, smem, s>>>(a);
   return cudaGetLastError();
 }
 // (threads, ctas_per_sm) -> instantiation; the second template argument only caps registers
 #define ALIGN_DISPATCH(FN, ...)                                                  \
   do {                                                                           \
+    if (threads == 32) return FN<32, 16>(__VA_ARGS__);                           \
     if (threads == 64) {                                                         \
       if (ctas > 12) return FN<64, 16>(__VA_ARGS__);                             \
       if (ctas > 8) return FN<64, 12>(__VA_ARGS__);                              \
@@ -535,11 +536,7 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
         ao.smem_seq_words = smem_orient ? c->max_pk_words : 0;
         CK(cudaMemsetAsync(a.next_pair, 0, sizeof(unsigned int), c->stream));
         CK(cudaEventRecord(c->ev[4], c->stream));
-        static size_t orient_configured = 0;
-        if (smem_orient > orient_configured) {
-          CK(cudaFuncSetAttribute(orient_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_orient));
-          orient_configured = smem_orient;
-        }
+        CK(cudaFuncSetAttribute(orient_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_orient));
         orient_kernel<128><<<cur_grid, 128, smem_orient, c->stream>>>(ao);
         CK(cudaGetLastError());
         CK(cudaEventRecord(c->ev[5], c->stream));
@@ -603,7 +600,27 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
       a.todo = c->d_todo.p;
       a.n_pairs = (uint32_t)todo.size();
     }
-    // accumulate stats from the final records of this chunk
+    // accumulate stats from the final records of this chunk. A pair may only stay failed for a reason
+    // the reference shares (ST_UNATTAINABLE = WF_STATUS_END_UNREACHABLE); a pair that hit a limit of
+    // this library's workspaces fails the whole call: the partition must never silently lack pairs
+    for (uint32_t i = 0; i < cn; ++i) {
+      const int st = h_out[i].status;
+      if (st == ST_UNATTAINABLE) {
+        c->stats.failed_pairs++;
+      } else if (st != ST_OK) {
+        char buf[256];
+        snprintf(buf, sizeof buf,
+                 "pair %llu (query %u, target %u) exceeds a workspace limit of the library (status %d: %s)",
+                 (unsigned long long)(first + i), h_out[i].q, h_out[i].t, st,
+                 st == ST_WS_BASE_OVERFLOW ? "base-case score above the full-memory capacity"
+                 : st == ST_WS_RUNS_OVERFLOW ? "run buffer overflow"
+                 : st == ST_STACK_OVERFLOW  ? "recursion stack overflow"
+                 : st == ST_RUNAWAY         ? "breakpoint search ran past its score bound"
+                                            : "not served after retries");
+        g_err = buf;
+        return SRGPU_E_INTERNAL;
+      }
+    }
     for (uint32_t i = 0; i < cn; ++i) {
       c->stats.wf_cells += h_out[i].cells;
       c->stats.orient_cells += h_out[i].ocells;

@@ -49,6 +49,8 @@ enum : int {
   ST_WS_BASE_OVERFLOW = 3,  // base-case score above full-memory capacity
   ST_WS_RUNS_OVERFLOW = 4,  // run buffer overflow
   ST_STACK_OVERFLOW = 5,
+  // 6 = ST_ARENA_OVERFLOW (kernels.cuh)
+  ST_RUNAWAY = 7,           // a breakpoint search ran past its score bound: a limit of this library, not a reference outcome
 };
 
 struct Penalties {
@@ -1516,7 +1518,7 @@ WFA_FN void wf_overlap(Ctx& cx, const Dir& d0, const Dir& d1, const Penalties& p
 // ---------------------------------------------------------------------------
 // Breakpoint search (WFA/wavefront_bialign.c:974-1082). Returns:
 //   0 = breakpoint found (in sh->bp), 1 = end reached (score in *score_reached),
-//   2 = workspace overflow, 3 = score bound exceeded (reported as unattainable).
+//   2 = workspace overflow, 3 = score bound exceeded (ST_RUNAWAY: the host fails the call loudly).
 // ---------------------------------------------------------------------------
 WFA_FN int wf_find_breakpoint(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, int* score_reached,
                               long long score_hint) {
@@ -1558,7 +1560,7 @@ WFA_FN int wf_find_breakpoint(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
   // scopes. score_hint bounds that penalty from above (sub-problems: the exact score the parent's
   // breakpoint assigned; level 0: what the edit-distance alignment of the strand choice would cost;
   // else deleting the pattern and inserting the text). A search that runs past the bound is broken
-  // (workspace corruption) and is reported as unattainable instead of spinning on.
+  // (workspace corruption) and is reported as ST_RUNAWAY instead of spinning on.
   long long score_bound = 2ll * imax(pen.o1, pen.o2) + (long long)(df.plen + df.tlen) * imax(pen.e1, pen.e2);
   if (score_hint < score_bound) score_bound = score_hint;
   score_bound += 4ll * pen.scope + 64;
@@ -1928,7 +1930,7 @@ WFA_FN PairResult wf_align_pair(Ctx& cx, const SeqView& sv, int plen, int tlen, 
       continue;
     }
     if (r == 3) {
-      if (cx.tid == 0) sh->status = ST_UNATTAINABLE;
+      if (cx.tid == 0) sh->status = ST_RUNAWAY;
       continue;
     }
     if (r == 1) {

@@ -73,3 +73,50 @@ def write_fasta(path, ids, seqs):
     with open(path, "wb") as f:
         for i, s in zip(ids, seqs):
             f.write(b">" + i.encode() + b"\n" + s.tobytes() + b"\n")
+
+
+def all_pairs(n: int) -> np.ndarray:
+    """n^2 ordered pairs, i-major, self pairs included (allwave/src/iterator.rs:37-46)."""
+    ii, jj = np.meshgrid(np.arange(n, dtype=np.uint32), np.arange(n, dtype=np.uint32), indexing="ij")
+    return np.ascontiguousarray(np.stack([ii.ravel(), jj.ravel()], axis=1), dtype=np.uint32)
+
+
+# Parity sets at the benchmarked configurations: tests/golden/bench_<name>.npz holds the reference's
+# outputs for exactly these inputs (scripts/make_golden_bench.py).
+BENCH_SETS = {
+    # name: (config, n taken from the front of the config's sequence list, description)
+    "c2": ("c2", 100, "BASELINE.json configs[1] in full: 100 x 50 kb, 1 %, all 10^4 ordered pairs"),
+    "c3s": ("c3", 40, "configs[2] slice: first 40 of 200 x 50 kb (20 % reverse-complemented, inversions), 1600 ordered pairs"),
+    "c4s": ("c4", 24, "configs[3] slice: first 24 of 1000 x 100 kb, 576 ordered pairs (256-thread launch shape)"),
+    "gmem": ("c2", 6, "6 x 52 kb with IUPAC bytes: 8-bit symbols, staged sequences exceed the shared-memory budget"),
+    "c5s": ("c5", 6, "configs[4] slice: first 6 of 2000 x 200 kb at 5 %, the 30 non-self ordered pairs"),
+}
+
+
+def bench_set(name: str):
+    """-> (ids, seqs, pairs, description) of a parity set. Sequences are a prefix of the named
+    config's list (make_sequences draws them one after another from one generator, so a prefix of
+    the full config is reproduced by asking for fewer)."""
+    cfg, n, desc = BENCH_SETS[name]
+    if name == "gmem":
+        ids, seqs = make_sequences(n, 52_000, 0.01, 77)
+        seqs = [s.copy() for s in seqs]
+        for k, s in enumerate(seqs):  # IUPAC codes and soft-masked stretches: byte equality, allwave RC -> 'N'
+            s[1000 + 10 * k:1004 + 10 * k] = np.frombuffer(b"RYKM", dtype=np.uint8)
+            s[20_000:20_050] = np.frombuffer(s[20_000:20_050].tobytes().lower(), dtype=np.uint8)
+        seqs[3] = np.ascontiguousarray(revcomp_iupac_safe(seqs[3]))
+        return ids, seqs, all_pairs(n), desc
+    ids, seqs = make_config(cfg, n=n)
+    pairs = all_pairs(n)
+    if name == "c5s":
+        pairs = np.ascontiguousarray(pairs[pairs[:, 0] != pairs[:, 1]])
+    return ids, seqs, pairs, desc
+
+
+def revcomp_iupac_safe(a: np.ndarray) -> np.ndarray:
+    """Reverse complement that keeps non-ACGT bytes as they are (so the set has a reverse-strand
+    sequence whose IUPAC bytes survive)."""
+    tbl = np.arange(256, dtype=np.uint8)
+    for x, y in zip(b"ACGTacgt", b"TGCAtgca"):
+        tbl[x] = y
+    return tbl[a[::-1]]

@@ -72,7 +72,11 @@ def built():
 def oracle(built):
     import _oracle
     if not os.path.exists(_oracle.ref_path()):
-        pytest.skip("oracle/_ref not built (needs /root/reference at build time)")
+        # never a silent skip: without the checker a parity test proves nothing. oracle/_ref is
+        # git-ignored but travels with the gpurun snapshot; build it with `make -C oracle` where
+        # /root/reference is mounted.
+        pytest.fail("oracle/_ref/%s is missing (build it with `make -C oracle` in the development container; "
+                    "it must travel to the GPU box with the snapshot)" % os.path.basename(_oracle.ref_path()))
     return _oracle.Oracle()
 
 

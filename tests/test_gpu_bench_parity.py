@@ -1,0 +1,82 @@
+"""Parity AT THE BENCHMARKED CONFIGURATIONS: the CUDA path through the C ABI against the reference's
+outputs committed in tests/golden/bench_<set>.npz (scripts/make_golden_bench.py: oracle/_ref =
+WFA2-lib + edlib compiled from the reference, plus the restated Rust glue), on the very inputs
+bench.py times. Bit-exact: strand, raw score, edit distance, CIGAR length and sha1 for EVERY ordered
+pair; unite-call count, component count, canonical partition sha1 and srgpu_uf_checksum per set.
+
+  c2    BASELINE.json configs[1] in full (10^4 pairs at 50 kb: the bench workload, 128x4 launch shape)
+  c3s   configs[2] slice, 40 x 50 kb with reverse-complemented sequences and inversions
+  c4s   configs[3] slice, 24 x 100 kb (the 256x2 launch shape used above 70 kb)
+  gmem  6 x 52 kb with IUPAC bytes: 8-bit symbols, sequences read from global memory (no staging)
+"""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN
+
+pytestmark = pytest.mark.gpu
+
+
+def load_bench_golden(name):
+    z = np.load(os.path.join(GOLDEN, "bench_%s.npz" % name))
+    meta = json.loads(bytes(z["meta"]).decode())
+    return meta, z
+
+
+@pytest.fixture(scope="module")
+def s(built):
+    import torch
+    assert torch.cuda.is_available(), "gpu tests need a CUDA device"
+    import seqrush_b200 as s
+    return s
+
+
+def seq_digest(seqs):
+    h = hashlib.sha1()
+    for a in seqs:
+        h.update(np.uint64(a.size).tobytes())
+        h.update(a.tobytes())
+    return h.hexdigest()
+
+
+@pytest.mark.parametrize("name", ["gmem", "c3s", "c4s", "c2"])
+def test_bench_set_matches_reference(s, name):
+    from seqrush_b200 import synth
+    meta, z = load_bench_golden(name)
+    ids, seqs, pairs, _ = synth.bench_set(name)
+    assert seq_digest(seqs) == meta["seq_sha1"], "synthetic inputs drifted from the ones the golden was made on"
+    assert np.array_equal(pairs, z["pairs"])
+    ctx = s.Context(0)
+    try:
+        # (1) every ordered pair through srgpu_align_pairs (the AllPairIterator -> AlignmentResult stream)
+        it = s.AllPairIterator([s.AllwaveSequence(i, a.tobytes()) for i, a in zip(ids, seqs)], s.AlignmentParams(), False,
+                               False, pairs=pairs, ctx=ctx)
+        k = 0
+        bad = []
+        for rs in it._batches(True, 1024):
+            for r in rs:
+                ok = (int(r.is_reverse) == int(z["is_reverse"][k]) and r.score == int(z["score"][k])
+                      and r.edit_distance == min(int(z["fwd_ed"][k]), int(z["rev_ed"][k]))
+                      and len(r.cigar_bytes) == int(z["cigar_len"][k])
+                      and hashlib.sha1(r.cigar_bytes).digest() == z["cigar_sha1"][k].tobytes())
+                if not ok:
+                    bad.append((k, int(pairs[k, 0]), int(pairs[k, 1])))
+                k += 1
+        assert k == pairs.shape[0]
+        assert not bad, "%d of %d pairs differ from the reference, first: %s" % (len(bad), k, bad[:5])
+        assert ctx.stats()["failed_pairs"] == 0
+        # (2) the fused path: align + CIGAR walk + unite, then the partition
+        sr = s.SeqRush([s.Sequence(i, a.tobytes()) for i, a in zip(ids, seqs)], ctx=ctx)
+        st = sr.align_and_unite(s.Args(min_match_length=meta["min_match_len"]), pairs=pairs)
+        assert st["failed_pairs"] == 0
+        assert st["unite_ops"] == meta["unite_calls"]
+        assert sr.count_components() == meta["components"]
+        assert "%016x" % sr.union_find.checksum() == meta["uf_checksum"]
+        canon = sr.canonical_partition()
+        assert hashlib.sha1(canon.astype("<u8").tobytes()).hexdigest() == meta["partition_sha1"]
+    finally:
+        ctx.close()
