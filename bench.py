@@ -1,15 +1,24 @@
 #!/usr/bin/env python
 """bench.py -- align+unite phase throughput on synthetic sequences (BASELINE.json metric).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c4s] [--impl ours|reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c4s|c4x] [--scaling weak|strong]
+                  [--impl ours|reference]
 
 A step = one pass of the hot path (strand choice + BiWFA + CIGAR walk + unite) over the whole
 ordered pair list of the workload. N>1 is launched by torch.distributed.run, one rank per GPU:
 pairs are dealt round-robin, each GPU unites into a private forest, and the step ends with the
 NCCL all_gather + device merge of the forests. Rank 0 prints ONE JSON line.
+
+Scaling. "weak" (default): ONE all-vs-all problem that grows with N so that per-GPU work stays
+fixed -- round(n0 * sqrt(N)) sequences of the workload's generator (the first n0 are the N=1
+workload), all ordered pairs, every pair aligned exactly once across the ranks. "strong": the N=1
+pair list split over N ranks (c4x: all 1000 x 100 kb sequences of BASELINE.json configs[3] resident,
+a fixed-seed sample of 8000 ordered pairs -- the full 10^6 pairs are hours per step on one GPU).
 """
 import argparse
+import glob
 import json
+import math
 import os
 import subprocess
 import sys
@@ -19,12 +28,16 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-# workloads: name -> (synth config, n, length, description)
+# workloads: name -> (synth config, n, length, pair sample (0 = all ordered pairs), golden parity set, description)
 WORKLOADS = {
-    "c2": ("c2", 100, 50_000, "synthetic 100 x 50 kb, 1% SNP/indel divergence per sequence, all 10^4 ordered pairs (BASELINE.json configs[1])"),
-    "c3": ("c3", 200, 50_000, "synthetic 200 x 50 kb, 20% reverse-complemented + inversions, all ordered pairs (configs[2])"),
-    "c4s": ("c4", 100, 100_000, "synthetic 100 x 100 kb slice of configs[3] (1000 x 100 kb), all ordered pairs"),
-    "tiny": ("c2", 16, 20_000, "synthetic 16 x 20 kb (debug)"),
+    "c2": ("c2", 100, 50_000, 0, "c2",
+           "synthetic 100 x 50 kb, 1% SNP/indel divergence per sequence, all 10^4 ordered pairs (BASELINE.json configs[1])"),
+    "c3": ("c3", 200, 50_000, 0, "c3s",
+           "synthetic 200 x 50 kb, 20% reverse-complemented + inversions, all ordered pairs (configs[2])"),
+    "c4s": ("c4", 100, 100_000, 0, "c4s", "synthetic 100 x 100 kb slice of configs[3] (1000 x 100 kb), all ordered pairs"),
+    "c4x": ("c4", 1000, 100_000, 8000, "c4s",
+            "synthetic 1000 x 100 kb, 1% (configs[3]): all sequences resident, fixed-seed sample of 8000 of the 10^6 ordered pairs"),
+    "tiny": ("c2", 16, 20_000, 0, None, "synthetic 16 x 20 kb (debug)"),
 }
 PEN = (5, 8, 2, 24, 1)  # seqrush -S 0,5,8,2,24,1 (src/seqrush.rs:45)
 
@@ -38,6 +51,20 @@ def load_peaks():
         except Exception:
             pass
     return 6650.0, 1965.0, "fallback"
+
+
+def latest_ncu_summary(kernel, workload):
+    """Newest committed ncu summary of a kernel (profiles/rNN?_ncu_<kernel>_<workload>.json, written from an
+    `ncu --set full` capture): DRAM bytes and wavefront cells / unite calls of the profiled launch."""
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_%s_%s.json" % (kernel, workload))))
+    if not files:
+        return None
+    try:
+        d = json.load(open(files[-1]))
+        d["file"] = os.path.relpath(files[-1], ROOT)
+        return d
+    except Exception:
+        return None
 
 
 class ClockSampler:
@@ -92,17 +119,62 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def make_workload(name):
-    from seqrush_b200 import synth
-    cfg, n, L, desc = WORKLOADS[name]
-    ids, seqs = synth.make_config(cfg, n=n, length=L)
-    return ids, seqs, desc
-
-
 def all_pairs(n):
+    from seqrush_b200 import synth
+    return synth.all_pairs(n)
+
+
+def make_workload(name, world=1, scaling="weak"):
+    """-> (ids, seqs, pairs, config dict). The config dict is the same in both arms (ours / reference)."""
     import numpy as np
-    ii, jj = np.meshgrid(np.arange(n, dtype=np.uint32), np.arange(n, dtype=np.uint32), indexing="ij")
-    return np.ascontiguousarray(np.stack([ii.ravel(), jj.ravel()], axis=1), dtype=np.uint32)
+    from seqrush_b200 import synth
+    cfg, n0, L, sample, _gold, desc = WORKLOADS[name]
+    n = n0
+    if world > 1 and scaling == "weak":
+        n = int(round(n0 * math.sqrt(world)))
+    ids, seqs = synth.make_config(cfg, n=n, length=L)
+    pairs = synth.all_pairs(n)
+    if sample and sample < pairs.shape[0]:
+        rng = np.random.default_rng(4242)
+        pairs = np.ascontiguousarray(pairs[np.sort(rng.choice(pairs.shape[0], size=sample, replace=False))])
+    bp = int(sum(int(seqs[int(q)].size) for q in pairs[:, 0]))
+    config = {
+        "workload": desc if n == n0 else desc + " -- weak scaling: grown to %d sequences (n0*sqrt(N)), all %d ordered pairs"
+                    % (n, pairs.shape[0]),
+        "name": name, "n_sequences": n, "penalties": "0,5,8,2,24,1", "min_match_len": 0,
+        "pairs_per_step": int(pairs.shape[0]), "aligned_Mbp_per_step": bp / 1e6,
+        "sharding": ("pairs round-robin over %d ranks, every pair aligned once, private forests merged by one "
+                     "all_gather_into_tensor + one device union pass" % world) if world > 1 else "single GPU",
+        "l2": "256 MB flush write between timed steps; per-CTA wavefront workspaces >> 126 MB L2",
+    }
+    return ids, seqs, pairs, config
+
+
+def host_cores():
+    logical = os.cpu_count() or 1
+    phys = set()
+    try:
+        pid = cid = None
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("physical id"):
+                pid = line.split(":")[1].strip()
+            elif line.startswith("core id"):
+                cid = line.split(":")[1].strip()
+            elif not line.strip():
+                if pid is not None and cid is not None:
+                    phys.add((pid, cid))
+                pid = cid = None
+    except OSError:
+        pass
+    return logical, (len(phys) or None)
+
+
+def cpu_sample_size(name, threads, seconds):
+    """Pairs for about `seconds` of work per thread, never fewer than 8 per thread (a pair of the
+    50 kb / 1 % shape costs ~0.28 core-seconds with oracle/_ref, growing with length^2)."""
+    L = WORKLOADS[name][2]
+    per_pair = 0.28 * (L / 50_000.0) ** 2
+    return threads * int(max(8, min(64, round(seconds / per_pair))))
 
 
 def cpu_baseline(seqs, pairs, sample_pairs, threads, seed=0):
@@ -112,7 +184,6 @@ def cpu_baseline(seqs, pairs, sample_pairs, threads, seed=0):
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import _oracle
     rng = np.random.default_rng(seed)
-    # sample among non-self pairs in proportion (self pairs are trivial); keep the n:n^2 ratio
     idx = rng.choice(pairs.shape[0], size=min(sample_pairs, pairs.shape[0]), replace=False)
     sub = pairs[np.sort(idx)]
     orc = _oracle.Oracle()
@@ -123,18 +194,24 @@ def cpu_baseline(seqs, pairs, sample_pairs, threads, seed=0):
     return st, sub.shape[0]
 
 
+def cpu_baseline_desc(ns, threads, phys):
+    return ("%d random ordered pairs of the workload (fixed seed, %d per thread), oracle/_ref = reference WFA2-lib + "
+            "edlib compiled from its sources + restated Rust glue, %d threads on %s physical cores"
+            % (ns, ns // max(1, threads), threads, phys if phys else "?"))
+
+
 def run_reference(args):
     """--impl reference: the reference's own CPU implementation of the path on the host cores."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    ids, seqs, desc = make_workload(args.workload)
-    pairs = all_pairs(len(seqs))
-    cores = os.cpu_count() or 1
-    sample = args.cpu_sample or max(cores, 64)
-    for _ in range(args.warmup and 1):
-        cpu_baseline(seqs, pairs, max(cores // 2, 4), cores, seed=99)
-    t0 = time.time()
+    world = int(os.environ.get("WORLD_SIZE", str(args.gpus)))
+    ids, seqs, pairs, config = make_workload(args.workload, world, args.scaling)
+    cores, phys = host_cores()
+    per_step_s = max(2.5, min(10.0, 150.0 / max(1, args.steps)))
+    sample = args.cpu_sample or cpu_sample_size(args.workload, cores, per_step_s)
+    for _ in range(1 if args.warmup else 0):
+        cpu_baseline(seqs, pairs, 2 * cores, cores, seed=99)
     bp = ops = 0
     secs = 0.0
     for k in range(args.steps):
@@ -146,12 +223,11 @@ def run_reference(args):
     out = {
         "impl": "reference", "metric": "aligned_Mbp_per_s", "value": val, "unit": "Mbp/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+        "scaling": args.scaling, "vs_baseline": None, "dtype": "int32", "data": "synthetic",
         "unite_ops_per_s": ops / secs,
-        "config": {"workload": desc, "penalties": "0,5,8,2,24,1", "min_match_len": 0},
-        "cpu_baseline": {"value": val, "unit": "Mbp/s", "cores": cores, "kind": "reference",
-                         "sample": "%d random ordered pairs of the workload per step (fixed seeds), oracle/_ref = "
-                                   "reference WFA2-lib + edlib compiled from its sources + restated Rust glue" % sample},
+        "config": config,
+        "cpu_baseline": {"value": val, "unit": "Mbp/s", "cores": cores, "physical_cores": phys, "kind": "reference",
+                         "sample": "per step: " + cpu_baseline_desc(ns, cores, phys)},
         "e2e": {"value": val, "unit": "Mbp/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     emit(out)
@@ -167,6 +243,43 @@ def emit(obj):
     f.flush()
 
 
+def golden_meta(name):
+    import numpy as np
+    p = os.path.join(ROOT, "tests", "golden", "bench_%s.npz" % name)
+    if not os.path.exists(p):
+        return None
+    return json.loads(bytes(np.load(p)["meta"]).decode())
+
+
+def parity_check(s, ctx, workload, world, scaling, checksum, comps, unite_ops_step):
+    """Compare with the reference's outputs committed under tests/golden/ (scripts/make_golden_bench.py).
+    The c2 workload IS a golden set (all 10^4 pairs): the partition of the timed steps is compared. For
+    the other workloads the golden is a slice of the same sequence list, run here once, untimed."""
+    gold = WORKLOADS[workload][4]
+    out = {"partition_checksum": "%016x" % checksum, "components": int(comps), "golden": None, "matches_golden": None}
+    if gold is None:
+        return out
+    meta = golden_meta(gold)
+    if meta is None:
+        return out
+    out["golden"] = "tests/golden/bench_%s.npz (%s)" % (gold, meta["description"])
+    if gold == workload and (world == 1 or scaling == "strong"):
+        out["matches_golden"] = bool("%016x" % checksum == meta["uf_checksum"] and comps == meta["components"]
+                                     and unite_ops_step == meta["unite_calls"])
+        out["compared"] = "partition checksum, component count and unite-call count of the timed steps"
+        return out
+    from seqrush_b200 import synth
+    ids, seqs, pairs, _ = synth.bench_set(gold)
+    sr = s.SeqRush([s.Sequence(i, a.tobytes()) for i, a in zip(ids, seqs)], ctx=ctx)
+    st = sr.align_and_unite(s.Args(min_match_length=0), pairs=pairs)
+    ok = ("%016x" % sr.union_find.checksum() == meta["uf_checksum"] and sr.count_components() == meta["components"]
+          and st["unite_ops"] == meta["unite_calls"] and st["failed_pairs"] == 0)
+    sr.union_find.close()
+    out["matches_golden"] = bool(ok)
+    out["compared"] = "golden slice run once before the timed region (same generator, same launch shape)"
+    return out
+
+
 def main():
     # stdout carries exactly one JSON line: anything else a library prints there (the NCCL version
     # banner, device printf) is sent to stderr by pointing fd 1 at fd 2 and keeping the original
@@ -179,6 +292,7 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--scaling", default=None, choices=["weak", "strong"])
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-sample", type=int, default=0)
     ap.add_argument("--threads", type=int, default=0)
@@ -186,6 +300,8 @@ def main():
     ap.add_argument("--ring", type=int, default=-1)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    if args.scaling is None:
+        args.scaling = "strong" if args.workload == "c4x" else "weak"
     if args.impl == "reference":
         return run_reference(args)
 
@@ -203,45 +319,39 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
     torch.cuda.set_device(local)
+    dev = "cuda:%d" % local
     dist = None
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
         trace("process group up")
 
-    ids, seqs, desc = make_workload(args.workload)
-    nseq = len(seqs)
-    pairs_all = all_pairs(nseq)
     from seqrush_b200.distributed import shard_pairs, merge_device_union_finds
-    # weak scaling: every rank runs the full pair list of its own replica of the workload?  No --
-    # the path shards: the ordered pair list is dealt round-robin, per-GPU work = pairs/N. To keep
-    # per-GPU work fixed as N grows ("weak"), the pair list is replicated N times (N passes of the
-    # workload), so each rank always aligns one full workload's worth of pairs.
-    job_pairs = np.concatenate([pairs_all] * world, axis=0) if world > 1 else pairs_all
-    my_pairs = shard_pairs(job_pairs, rank, world)
-
     stream = torch.cuda.Stream()
     ctx = s.Context(local, stream.cuda_stream)
     if args.threads or args.ctas_per_sm or args.ring >= 0:
         ctx.configure(threads=args.threads, ctas_per_sm=args.ctas_per_sm, ring_diagonals=args.ring)
+
+    ids, seqs, job_pairs, config = make_workload(args.workload, world, args.scaling)
+    my_pairs = shard_pairs(job_pairs, rank, world)
     sr = s.SeqRush([s.Sequence(i, a.tobytes()) for i, a in zip(ids, seqs)], ctx=ctx)
     total_len = sr.total_length
-    d_pairs = torch.from_numpy(my_pairs.view(np.int32).copy()).to("cuda:%d" % local)
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda:%d" % local)
+    d_pairs = torch.from_numpy(my_pairs.view(np.int32).copy()).to(dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     sargs = s.Args(min_match_length=0)
 
     def reset_uf():
         sr.union_find.clear()  # UFRush::clear, then SeqRush::new's unite(2i, 2i+1) loop (src/seqrush.rs:324-328)
         sr.union_find.unite_fr_all(total_len)
 
-    def step_device():
+    def step_device(tm=None):
         reset_uf()
-        trace("union-find reset")
         st = sr.align_and_unite_device(d_pairs.data_ptr(), my_pairs.shape[0], sargs)
         trace("align+unite done: %.0f ms align, %d launches, %d retries" % (st["align_ms"], st["kernel_launches"], st["retries"]))
+        if st["failed_pairs"]:
+            raise SystemExit("bench: %d pairs failed" % st["failed_pairs"])
         if dist is not None:
-            merge_device_union_finds(sr.union_find, dist)
-            trace("forests merged")
+            merge_device_union_finds(sr.union_find, dist, tm)
         return st
 
     def barrier():
@@ -253,31 +363,36 @@ def main():
     trace("sequences resident, %d pairs on this rank" % my_pairs.shape[0])
     for _ in range(args.warmup):
         step_device()
-        trace("warm-up step done")
         flush.fill_(1)
     barrier()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    agg = {"align_ms": 0.0, "union_ms": 0.0, "orient_ms": 0.0, "wf_cells": 0, "orient_cells": 0, "unite_ops": 0, "unite_links": 0,
-           "launches": 0, "aligned_bp": 0, "align_launches": 0, "union_launches": 0}
-    step_ms = []
+    keys = ("align_ms", "union_ms", "orient_ms", "wf_cells", "orient_cells", "unite_ops", "unite_links", "aligned_bp",
+            "align_launches", "union_launches")
+    agg = {k: 0 for k in keys}
+    agg["launches"] = 0
+    step_ms, merge_ms, gathered_bytes = [], [], 0
     for k in range(args.steps):
         flush.fill_(k & 255)  # L2 flush between timed iterations (256 MB > 126 MB L2); outside the timed events
         barrier()
+        tm = {}
         e0.record(stream)
-        st = step_device()
+        st = step_device(tm)
         e1.record(stream)
         barrier()
         step_ms.append(e0.elapsed_time(e1))
-        trace("timed step %d: %.1f ms" % (k, step_ms[-1]))
-        for kk in ("align_ms", "union_ms", "orient_ms", "wf_cells", "orient_cells", "unite_ops", "unite_links", "aligned_bp",
-                   "align_launches", "union_launches"):
+        if "events" in tm:
+            ev = tm["events"]
+            merge_ms.append((ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2])))
+            gathered_bytes = tm["gathered_bytes"]
+        for kk in keys:
             agg[kk] += st[kk]
-        agg["launches"] += st["kernel_launches"] + 3  # + uf init, unite_fr_all, (compress/merge counted below)
+        # + uf clear, unite_fr_all, and (N>1) compress, merge, compress of the exchange
+        agg["launches"] += st["kernel_launches"] + 2 + (3 if dist is not None else 0)
     clocks = sampler.stop() if rank == 0 else None
-    t = torch.tensor([sum(step_ms)], dtype=torch.float64, device="cuda:%d" % local)
+    t = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     total_ms = float(t.item())
@@ -301,19 +416,26 @@ def main():
         e1.record(stream)
         barrier()
         e2e_ms.append(e0.elapsed_time(e1))
-        trace("e2e step %d: %.1f ms" % (k, e2e_ms[-1]))
         sr2.union_find.close()
-    t = torch.tensor([sum(e2e_ms) / len(e2e_ms)], dtype=torch.float64, device="cuda:%d" % local)
+    t = torch.tensor([sum(e2e_ms) / len(e2e_ms)], dtype=torch.float64, device=dev)
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_step_ms = float(t.item())
 
-    # totals over ranks
+    # totals / extremes over ranks
     tot = torch.tensor([agg["aligned_bp"], agg["unite_ops"], agg["wf_cells"], agg["orient_cells"], agg["unite_links"]],
-                       dtype=torch.float64, device="cuda:%d" % local)
+                       dtype=torch.float64, device=dev)
+    al = torch.tensor([agg["align_ms"] + agg["orient_ms"]], dtype=torch.float64, device=dev)
+    al_min, al_max = al.clone(), al.clone()
     if dist is not None:
         dist.all_reduce(tot)
+        dist.all_reduce(al_min, op=dist.ReduceOp.MIN)
+        dist.all_reduce(al_max, op=dist.ReduceOp.MAX)
     bp, ops, cells, ocells, links = [float(x) for x in tot.tolist()]
+    parity = parity_check(s, ctx, args.workload, world, args.scaling, checksum, comps, int(round(ops / args.steps))) \
+        if rank == 0 else None
+    if dist is not None:
+        dist.barrier()
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -325,59 +447,67 @@ def main():
     # roofline of the dominant kernel (align_kernel), rank 0's launches, device time from CUDA events
     # recorded by the library on its launch stream (srgpu_stats.align_ms)
     al_s = agg["align_ms"] / 1e3
-    r0_cells, r0_ocells = agg["wf_cells"], agg["orient_cells"]
+    r0_cells = agg["wf_cells"]
     n_launch = max(1, agg["align_launches"])
-    BYTES_PER_CELL = 48  # 7 source offsets read + 5 offsets written, int32 (DESIGN.md "roofline")
-    # measured DRAM traffic of the align kernel per wavefront cell: dram__bytes_read.sum + dram__bytes_write.sum
-    # = 855.5 GB over the 2.052e10 cells of a 600-pair c2 launch (ncu --set full, profiles/r01j_ncu_align_kernel_c2.txt);
-    # scaled by this launch's cell count because the full launch is too long to replay under ncu
-    DRAM_BYTES_PER_CELL_NCU = 855.5e9 / 2.052e10
-    alg_bytes = BYTES_PER_CELL * r0_cells  # the strand choice runs in its own (small) launch: orient_kernel
     INT_OPS_PER_CELL = 17 + 6  # 17 int ops per cell + 6 per extend word (>= 1 word per cell)
     int_peak = 148 * 4 * 32 * sm_max_mhz * 1e6
+    DESIGN_BYTES_PER_CELL = 48  # what THIS design moves through L2/HBM per cell: 7 source offsets read + 5 written, int32
+    prof = latest_ncu_summary("align_kernel", "c2")
+    traffic = None
+    if prof and prof.get("cells"):
+        traffic = (prof["dram_bytes_read"] + prof["dram_bytes_write"]) / prof["cells"] * r0_cells / n_launch
     un_s = max(agg["union_ms"] / 1e3, 1e-9)
     r0_ops, r0_links = agg["unite_ops"], agg["unite_links"]
     out = {
         "metric": "aligned_Mbp_per_s", "value": value, "unit": "Mbp/s", "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": args.scaling,
         "vs_baseline": None, "dtype": "int32", "data": "synthetic",
         "unite_ops_per_s": ops / secs,
-        "config": {"workload": desc, "penalties": "0,5,8,2,24,1", "min_match_len": 0,
-                   "pairs_per_step": int(job_pairs.shape[0]), "aligned_Mbp_per_step": job_bp_step / 1e6,
-                   "sharding": "pairs round-robin over ranks, forests merged by all_gather + device union" if world > 1 else "single GPU",
-                   "l2": "256 MB flush write between timed steps; per-CTA wavefront workspaces >> 126 MB L2"},
+        "config": config,
         "e2e": {"value": job_bp_step / 1e6 / (e2e_step_ms / 1e3), "unit": "Mbp/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "ms_per_step": e2e_step_ms},
         "gpu_launches": int(agg["launches"]),
         "clocks": clocks,
-        "roofline": {"kernel": "align_kernel (orientation + BiWFA + backtrace)", "bound": "hbm",
-                     "achieved": alg_bytes / al_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": alg_bytes / al_s / 1e9 / hbm_peak,
-                     "traffic": DRAM_BYTES_PER_CELL_NCU * r0_cells / n_launch if args.workload == "c2" else None,
-                     "traffic_unit": "bytes per launch (ncu-measured bytes per cell x cells of this launch)",
-                     "peak_kind": peak_kind,
-                     "algorithmic_bytes_per_launch": alg_bytes / n_launch, "avg_launch_ms": agg["align_ms"] / n_launch,
+        # primary roofline: integer issue, 23 lane-ops per wavefront cell against 148 SMs x 4 x 32 lanes
+        "roofline": {"kernel": "align_kernel (BiWFA gap-affine-2p + backtrace)", "bound": "int_issue",
+                     "achieved": INT_OPS_PER_CELL * r0_cells / al_s / 1e9, "peak": int_peak / 1e9, "unit": "Gop/s",
+                     "frac": INT_OPS_PER_CELL * r0_cells / al_s / int_peak,
+                     "cells_per_s": r0_cells / al_s, "algorithmic_ops_per_launch": INT_OPS_PER_CELL * r0_cells / n_launch,
+                     "traffic": traffic,
+                     "traffic_note": ("DRAM bytes per launch = dram__bytes_read+write per wavefront cell of the newest committed "
+                                      "ncu --set full capture (%s) x the cells of this launch; the full launch is too long to "
+                                      "replay under ncu" % (prof["file"] if prof else "none")),
+                     "peak_kind": "148 SMs x 4 schedulers x 32 lanes x %s sm clock" % peak_kind,
+                     "avg_launch_ms": agg["align_ms"] / n_launch,
                      "share_of_step": agg["align_ms"] / sum(step_ms),
                      "orient_kernel_share_of_step": agg["orient_ms"] / sum(step_ms)},
-        "roofline_int_issue": {"kernel": "align_kernel", "bound": "int_issue",
-                               "achieved": INT_OPS_PER_CELL * r0_cells / al_s / 1e9,
-                               "peak": int_peak / 1e9, "unit": "Gop/s",
-                               "frac": INT_OPS_PER_CELL * r0_cells / al_s / int_peak,
-                               "cells_per_s": r0_cells / al_s},
+        # the same launches against HBM under this design's traffic model (NOT algorithmic bytes: the rings live in HBM)
+        "roofline_hbm_design_traffic": {"kernel": "align_kernel", "bound": "hbm",
+                                        "achieved": DESIGN_BYTES_PER_CELL * r0_cells / al_s / 1e9, "peak": hbm_peak,
+                                        "unit": "GB/s", "frac": DESIGN_BYTES_PER_CELL * r0_cells / al_s / 1e9 / hbm_peak,
+                                        "bytes_per_cell": DESIGN_BYTES_PER_CELL, "peak_kind": peak_kind},
+        "roofline_orient": {"kernel": "orient_kernel (lock-step unit-cost WFA on both strands)", "bound": "int_issue",
+                            "cells_per_s": agg["orient_cells"] / max(agg["orient_ms"] / 1e3, 1e-9),
+                            "frac": 8 * agg["orient_cells"] / max(agg["orient_ms"] / 1e3, 1e-9) / int_peak,
+                            "ops_per_cell": 8, "avg_launch_ms": agg["orient_ms"] / n_launch},
         "roofline_union": {"kernel": "union_kernel", "bound": "hbm",
                            "achieved": (r0_ops * 8 + r0_links * 4) / un_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
                            "frac": (r0_ops * 8 + r0_links * 4) / un_s / 1e9 / hbm_peak,
                            "unite_ops_per_s_kernel": r0_ops / un_s, "avg_launch_ms": agg["union_ms"] / max(1, agg["union_launches"])},
-        "parity": {"partition_checksum": "%016x" % checksum, "components": int(comps)},
+        "parity": parity,
     }
+    if world > 1:
+        out["multi_gpu"] = {"align_ms_per_rank_min": float(al_min.item()) / args.steps,
+                            "align_ms_per_rank_max": float(al_max.item()) / args.steps,
+                            "gather_ms": sum(m[0] for m in merge_ms) / max(1, len(merge_ms)),
+                            "merge_ms": sum(m[1] for m in merge_ms) / max(1, len(merge_ms)),
+                            "gathered_bytes_per_rank": gathered_bytes}
     if not args.no_cpu_baseline and world == 1:
-        cores = os.cpu_count() or 1
-        sample = args.cpu_sample or max(cores, 64)
-        st, ns = cpu_baseline(seqs, pairs_all, sample, cores)
+        cores, phys = host_cores()
+        sample = args.cpu_sample or cpu_sample_size(args.workload, cores, 12.0)
+        st, ns = cpu_baseline(seqs, job_pairs, sample, cores)
         out["cpu_baseline"] = {"value": st["aligned_bp"] / 1e6 / st["seconds"], "unit": "Mbp/s", "cores": cores,
-                               "kind": "reference",
-                               "sample": "%d random ordered pairs of the workload, oracle/_ref (reference WFA2-lib + "
-                                         "edlib compiled from its sources) + restated Rust glue, %d threads" % (ns, cores),
+                               "physical_cores": phys, "kind": "reference", "sample": cpu_baseline_desc(ns, cores, phys),
                                "unite_ops_per_s": st["unite_calls"] / st["seconds"]}
     emit(out)
     if dist is not None:

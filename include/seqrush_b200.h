@@ -23,7 +23,8 @@ extern "C" {
 #define SRGPU_E_CUDA (-1)      /* CUDA runtime error (no device, OOM, launch failure) */
 #define SRGPU_E_ARG (-2)       /* invalid argument (index out of range, bad penalties) */
 #define SRGPU_E_RANGE (-3)     /* Pos outside the union-find (reference: assert in uf_rush lib.rs:113) */
-#define SRGPU_E_VALIDATE (-4)  /* "unite non-matching bases" (reference: panic in validate_match, src/seqrush.rs:1184-1205) */
+/* (-4 was SRGPU_E_VALIDATE, the reference's validate_match panic, src/seqrush.rs:1184-1205. No entry point can
+ * produce it: every CIGAR walk builds its match runs from bases that compared equal, so it was removed.) */
 #define SRGPU_E_INTERNAL (-5)
 
 /* Per-pair status in srgpu_result.status */
@@ -104,6 +105,9 @@ const char* srgpu_last_error(void);
 int srgpu_ctx_create(int device, void* stream, srgpu_ctx** out);
 void srgpu_ctx_destroy(srgpu_ctx* ctx);
 int srgpu_ctx_synchronize(srgpu_ctx* ctx);
+/* The cudaStream_t every launch of this context goes to (so a host can order its own work, e.g. an
+ * NCCL collective, against it without a host synchronisation). */
+void* srgpu_ctx_stream(srgpu_ctx* ctx);
 /* Tunables: threads per CTA (multiple of 32), CTAs per SM, initial ring width in diagonals
  * (0 = automatic). */
 int srgpu_ctx_configure(srgpu_ctx* ctx, int threads, int ctas_per_sm, int ring_diagonals);
@@ -132,9 +136,29 @@ int srgpu_align_and_unite(srgpu_ctx* ctx, srgpu_uf* uf, const uint32_t (*pairs)[
 int srgpu_align_and_unite_device(srgpu_ctx* ctx, srgpu_uf* uf, const void* d_pairs, uint64_t n_pairs,
                                  const srgpu_penalties* pen, uint64_t min_match_len);
 
+/* srgpu_align_pairs that also unites: ONE alignment pass yields the CIGARs (for the PAF of
+ * --output-alignments) and feeds the union-find, where the reference aligns every pair twice
+ * (src/seqrush.rs:693-716 then :728-756). The unions run on the device from the run-length CIGARs
+ * before they are expanded to bytes. */
+int srgpu_align_pairs_and_unite(srgpu_ctx* ctx, srgpu_uf* uf, const uint32_t (*pairs)[2], uint64_t n_pairs,
+                                const srgpu_penalties* pen, uint64_t min_match_len, srgpu_result* out,
+                                uint8_t** cigar_arena, uint64_t* cigar_arena_len);
+
 /* Replacement of process_alignment alone (src/seqrush.rs:1134-1481) for CIGARs that come from
  * elsewhere (the --paf path, src/seqrush.rs:510-609): cigar is the RLE string ("12=1X3I..."),
- * 'M' and '=' are re-checked base by base like the reference. */
+ * 'M' and '=' are re-checked base by base like the reference (so the reference's validate_match
+ * panic, :1179-1207, has no counterpart: a run is built only from bases that compared equal).
+ * The batched form takes every record of a PAF file in one call: the strings are parsed into run
+ * lists on the host and walked by one multi-CTA launch. */
+typedef struct {
+  uint32_t query_idx, target_idx;
+  int32_t query_is_rc; /* PAF strand == '-' (src/seqrush.rs:580) */
+  int32_t reserved;
+  uint64_t query_start, target_start; /* PAF columns 3 and 8 */
+  const char* cigar;                  /* NUL-terminated RLE string of the cg:Z: tag ("" when absent, :552-555) */
+} srgpu_paf_record;
+int srgpu_process_alignments(srgpu_ctx* ctx, srgpu_uf* uf, const srgpu_paf_record* records, uint64_t n_records,
+                             uint64_t min_match_len);
 int srgpu_process_alignment(srgpu_ctx* ctx, srgpu_uf* uf, const char* cigar, uint32_t query_idx, uint32_t target_idx,
                             uint64_t min_match_len, int query_is_rc, uint64_t query_start, uint64_t target_start);
 
@@ -177,6 +201,11 @@ int srgpu_uf_checksum(srgpu_uf* uf, uint64_t* checksum);
 void* srgpu_uf_device_ptr(srgpu_uf* uf);
 int srgpu_uf_compress(srgpu_uf* uf);
 int srgpu_uf_merge_roots(srgpu_uf* uf, const void* d_peer_roots, uint64_t n);
+/* Stream-ordered forms for the end-of-step exchange (no host synchronisation): compress, then -- after
+ * an all_gather of every rank's compressed parent array into one [world][n] device buffer -- ONE pass
+ * that unites (p, gathered[r][p]) for every peer r != my_rank. */
+int srgpu_uf_compress_async(srgpu_uf* uf);
+int srgpu_uf_merge_gathered(srgpu_uf* uf, const void* d_gathered, uint64_t n, int world, int my_rank);
 
 #ifdef __cplusplus
 }

@@ -17,9 +17,11 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 
 # every symbol include/seqrush_b200.h declares (checked by tests/test_abi.py)
 EXPORTS = [
-    "srgpu_last_error", "srgpu_ctx_create", "srgpu_ctx_destroy", "srgpu_ctx_synchronize", "srgpu_ctx_configure",
+    "srgpu_last_error", "srgpu_ctx_create", "srgpu_ctx_destroy", "srgpu_ctx_synchronize", "srgpu_ctx_stream",
+    "srgpu_ctx_configure", "srgpu_uf_compress_async", "srgpu_uf_merge_gathered",
     "srgpu_ctx_stats", "srgpu_set_sequences", "srgpu_total_length", "srgpu_align_pairs", "srgpu_free",
-    "srgpu_align_and_unite", "srgpu_align_and_unite_device", "srgpu_process_alignment", "srgpu_uf_new",
+    "srgpu_align_and_unite", "srgpu_align_and_unite_device", "srgpu_align_pairs_and_unite",
+    "srgpu_process_alignment", "srgpu_process_alignments", "srgpu_uf_new",
     "srgpu_uf_free", "srgpu_uf_capacity", "srgpu_uf_clear", "srgpu_uf_find", "srgpu_uf_same", "srgpu_uf_unite",
     "srgpu_uf_unite_matching_region", "srgpu_uf_unite_matching_region_seq2_rc", "srgpu_uf_unite_regions",
     "srgpu_uf_unite_fr_all", "srgpu_uf_roots", "srgpu_uf_count_components", "srgpu_uf_checksum",
@@ -78,6 +80,12 @@ class Region(C.Structure):
                 ("seq1_is_rc", C.c_int32), ("seq2_rc_form", C.c_int32)]
 
 
+class PafRecord(C.Structure):
+    _fields_ = [("query_idx", C.c_uint32), ("target_idx", C.c_uint32), ("query_is_rc", C.c_int32),
+                ("reserved", C.c_int32), ("query_start", C.c_uint64), ("target_start", C.c_uint64),
+                ("cigar", C.c_char_p)]
+
+
 _lib = None
 
 
@@ -113,6 +121,9 @@ def lib():
     L.srgpu_align_and_unite.argtypes = [vp, vp, vp, u64, C.POINTER(Penalties), u64, C.POINTER(Result)]
     L.srgpu_align_and_unite_device.argtypes = [vp, vp, vp, u64, C.POINTER(Penalties), u64]
     L.srgpu_process_alignment.argtypes = [vp, vp, C.c_char_p, u32, u32, u64, i32, u64, u64]
+    L.srgpu_process_alignments.argtypes = [vp, vp, C.POINTER(PafRecord), u64, u64]
+    L.srgpu_align_pairs_and_unite.argtypes = [vp, vp, vp, u64, C.POINTER(Penalties), u64, C.POINTER(Result),
+                                              C.POINTER(vp), C.POINTER(u64)]
     L.srgpu_uf_new.argtypes = [vp, u64, C.POINTER(vp)]
     L.srgpu_uf_free.argtypes = [vp]
     L.srgpu_uf_free.restype = None
@@ -133,6 +144,10 @@ def lib():
     L.srgpu_uf_device_ptr.restype = vp
     L.srgpu_uf_compress.argtypes = [vp]
     L.srgpu_uf_merge_roots.argtypes = [vp, vp, u64]
+    L.srgpu_uf_compress_async.argtypes = [vp]
+    L.srgpu_uf_merge_gathered.argtypes = [vp, vp, u64, i32, i32]
+    L.srgpu_ctx_stream.argtypes = [vp]
+    L.srgpu_ctx_stream.restype = vp
     _lib = L
     return L
 

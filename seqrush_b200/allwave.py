@@ -136,7 +136,10 @@ class AllPairIterator:
             out.extend(r)
         return out
 
-    def _batches(self, want_cigars, batch):
+    def _batches(self, want_cigars, batch, unite_into=None, min_match_len=0):
+        """Batches of AlignmentResult in pair order. With ``unite_into`` (a BidirectedUnionFind on the
+        same context) every batch is also united on the device from the same alignment pass
+        (srgpu_align_pairs_and_unite)."""
         L = _lib.lib()
         if not self._uploaded:
             self.ctx.set_sequences([s.seq for s in self.sequences])
@@ -148,8 +151,13 @@ class AllPairIterator:
             res = (_lib.Result * n)()
             arena = C.c_void_p()
             alen = C.c_uint64()
-            _lib.check(L.srgpu_align_pairs(self.ctx._h, pr.ctypes.data, n, C.byref(pen), res,
-                                           C.byref(arena) if want_cigars else None, C.byref(alen)))
+            if unite_into is None:
+                _lib.check(L.srgpu_align_pairs(self.ctx._h, pr.ctypes.data, n, C.byref(pen), res,
+                                               C.byref(arena) if want_cigars else None, C.byref(alen)))
+            else:
+                _lib.check(L.srgpu_align_pairs_and_unite(self.ctx._h, unite_into._h, pr.ctypes.data, n, C.byref(pen),
+                                                         min_match_len, res, C.byref(arena) if want_cigars else None,
+                                                         C.byref(alen)))
             buf = C.string_at(arena, alen.value) if want_cigars and arena.value else b""
             if arena.value:
                 L.srgpu_free(arena)

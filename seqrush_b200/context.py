@@ -34,6 +34,10 @@ class Context:
     def configure(self, threads=0, ctas_per_sm=0, ring_diagonals=-1):
         _lib.check(_lib.lib().srgpu_ctx_configure(self._h, threads, ctas_per_sm, ring_diagonals))
 
+    def stream_ptr(self) -> int:
+        """cudaStream_t of every launch of this context."""
+        return int(_lib.lib().srgpu_ctx_stream(self._h) or 0)
+
     def synchronize(self):
         _lib.check(_lib.lib().srgpu_ctx_synchronize(self._h))
 

@@ -83,7 +83,8 @@ struct srgpu_ctx {
   DevBuf<uint32_t> d_pk_fwd, d_pk_rc;
   int lbits = 3;              // log2(bits per packed symbol): 1, 2 or 3
   uint32_t max_pk_words = 0;  // packed words of the longest sequence incl. guards
-  int smem_budget = 96 * 1024;  // dynamic shared memory the align kernel may use for staged sequences
+  int smem_budget = 96 * 1024;  // dynamic shared memory a kernel may use for staged sequences
+  bool stage_seqs = false;      // align_kernel: also stage the two sequences (SRGPU_STAGE_SEQS=1)
   DevBuf<uint32_t> d_len;
   std::vector<uint32_t> h_len;
   std::vector<uint64_t> h_pos_off;
@@ -97,7 +98,8 @@ struct srgpu_ctx {
   DevBuf<unsigned long long> d_scalars;  // [0] arena_head, [1] next_pair(uint) , [4..8] counters
   DevBuf<unsigned long long> d_byteoff;
   DevBuf<uint8_t> d_bytes;
-  DevBuf<char> d_cigar_str;
+  DevBuf<PafRecordDev> d_paf_recs;
+  DevBuf<unsigned long long> d_paf_runs;
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   srgpu_stats stats{};
   std::vector<srgpu_uf*> ufs;  // union-finds living on this context (orphaned when it is destroyed)
@@ -154,6 +156,7 @@ extern "C" int srgpu_ctx_create(int device, void* stream, srgpu_ctx** out) {
   }
   for (int i = 0; i < 6; ++i) CK(cudaEventCreate(&c->ev[i]));
   if (const char* e = getenv("SRGPU_SMEM_BUDGET")) c->smem_budget = atoi(e);  // tuning: 0 = never stage sequences
+  if (const char* e = getenv("SRGPU_STAGE_SEQS")) c->stage_seqs = atoi(e) != 0;
   *out = c;
   return SRGPU_OK;
 }
@@ -170,11 +173,13 @@ extern "C" void srgpu_ctx_destroy(srgpu_ctx* c) {
   c->d_fwd.release(); c->d_pk_fwd.release(); c->d_pk_rc.release(); c->d_pk_off.release(); c->d_rcsafe.release(); c->d_byte_off.release(); c->d_pos_off.release();
   c->d_len.release(); c->d_ring.release(); c->d_full.release(); c->d_orient.release(); c->d_full_meta.release();
   c->d_runs_tmp.release(); c->d_bt_tmp.release(); c->d_pairs.release(); c->d_out.release(); c->d_arena.release();
-  c->d_todo.release(); c->d_scalars.release(); c->d_byteoff.release(); c->d_bytes.release(); c->d_cigar_str.release();
+  c->d_todo.release(); c->d_scalars.release(); c->d_byteoff.release(); c->d_bytes.release(); c->d_paf_recs.release(); c->d_paf_runs.release();
   for (int i = 0; i < 6; ++i) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
   if (c->own_stream) cudaStreamDestroy(c->stream);
   delete c;
 }
+
+extern "C" void* srgpu_ctx_stream(srgpu_ctx* c) { return c ? (void*)c->stream : nullptr; }
 
 extern "C" int srgpu_ctx_synchronize(srgpu_ctx* c) {
   if (!c) return SRGPU_E_ARG;
@@ -422,14 +427,17 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
     return SRGPU_E_ARG;
   }
   const uint32_t maxlen = c->max_len;
-  // staged sequences: three packed sequences per CTA in dynamic shared memory when they fit
-  // align_kernel stages two packed sequences (chosen query strand, target), orient_kernel three
-  size_t smem = (size_t)2 * c->max_pk_words * 4;
+  // orient_kernel stages its three packed sequences (query forward, query RC, target) in dynamic shared
+  // memory when they fit. align_kernel reads its two sequences from global memory through L1 (measured
+  // on the 1500-pair c2 slice: 873 ms against 845 ms staged, profiles/r02a_*) and spends its shared
+  // memory on the double-buffered row staging of the score step instead; SRGPU_STAGE_SEQS=1 stages them
+  // as well when both fit the budget.
+  size_t smem_seqs = (size_t)2 * c->max_pk_words * 4;
   size_t smem_orient = (size_t)3 * c->max_pk_words * 4;
   uint32_t smem_seq_words = c->max_pk_words;
   if (smem_orient > (size_t)c->smem_budget) smem_orient = 0;
-  if (smem > (size_t)c->smem_budget) {
-    smem = 0;
+  if (!c->stage_seqs || smem_seqs > (size_t)c->smem_budget) {
+    smem_seqs = 0;
     smem_seq_words = 0;
   }
   // launch shape: 128 threads x 4 CTAs/SM up to ~70 kb; longer sequences have wavefronts wide enough to
@@ -440,6 +448,7 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
     threads = 256;
     ctas_per_sm = 2;
   }
+  const size_t smem = smem_seqs + (size_t)(threads / 32) * 2 * STAGE_INTS * sizeof(int32_t);
   const int resident = std::min(ctas_per_sm, align_occupancy(threads, ctas_per_sm, smem));
   int grid = c->n_sm * resident;
   if ((uint64_t)grid > n_pairs) grid = (int)n_pairs;
@@ -673,19 +682,33 @@ static int upload_pairs(srgpu_ctx* c, const uint32_t (*pairs)[2], uint64_t n_pai
   return 0;
 }
 
+static int check_uf(srgpu_ctx* c, srgpu_uf* uf);
+static int align_pairs_impl(srgpu_ctx* c, srgpu_uf* uf, uint64_t min_match_len, const uint32_t (*pairs)[2], uint64_t n_pairs,
+                            const srgpu_penalties* pen, srgpu_result* out, uint8_t** cigar_arena, uint64_t* cigar_arena_len);
 extern "C" int srgpu_align_pairs(srgpu_ctx* c, const uint32_t (*pairs)[2], uint64_t n_pairs, const srgpu_penalties* pen,
                                  srgpu_result* out, uint8_t** cigar_arena, uint64_t* cigar_arena_len) {
+  return align_pairs_impl(c, nullptr, 0, pairs, n_pairs, pen, out, cigar_arena, cigar_arena_len);
+}
+extern "C" int srgpu_align_pairs_and_unite(srgpu_ctx* c, srgpu_uf* uf, const uint32_t (*pairs)[2], uint64_t n_pairs,
+                                           const srgpu_penalties* pen, uint64_t min_match_len, srgpu_result* out,
+                                           uint8_t** cigar_arena, uint64_t* cigar_arena_len) {
+  if (!uf) return SRGPU_E_ARG;
+  return align_pairs_impl(c, uf, min_match_len, pairs, n_pairs, pen, out, cigar_arena, cigar_arena_len);
+}
+static int align_pairs_impl(srgpu_ctx* c, srgpu_uf* uf, uint64_t min_match_len, const uint32_t (*pairs)[2], uint64_t n_pairs,
+                            const srgpu_penalties* pen, srgpu_result* out, uint8_t** cigar_arena, uint64_t* cigar_arena_len) {
   if (!c || (!pairs && n_pairs) || !out) return SRGPU_E_ARG;
   std::lock_guard<std::mutex> lk(c->mu);
   CK(cudaSetDevice(c->device));
   Penalties p;
   int rc;
   if ((rc = check_penalties(pen, &p))) return rc;
+  if (uf && (rc = check_uf(c, uf))) return rc;
   if (cigar_arena) *cigar_arena = nullptr;
   if (cigar_arena_len) *cigar_arena_len = 0;
   if (n_pairs == 0) return SRGPU_OK;
   if ((rc = upload_pairs(c, pairs, n_pairs))) return rc;
-  if ((rc = run_pairs(c, nullptr, c->d_pairs.p, n_pairs, p, 0, cigar_arena != nullptr))) return rc;
+  if ((rc = run_pairs(c, uf, c->d_pairs.p, n_pairs, p, min_match_len, cigar_arena != nullptr))) return rc;
   std::vector<PairOut> h(n_pairs);
   CK(cudaMemcpy(h.data(), c->d_out.p, n_pairs * sizeof(PairOut), cudaMemcpyDeviceToHost));
   std::vector<unsigned long long> boff(n_pairs);
@@ -764,25 +787,94 @@ extern "C" int srgpu_align_and_unite_device(srgpu_ctx* c, srgpu_uf* uf, const vo
   return run_pairs(c, uf, (const uint2*)d_pairs, n_pairs, p, min_match_len, false);
 }
 
-extern "C" int srgpu_process_alignment(srgpu_ctx* c, srgpu_uf* uf, const char* cigar, uint32_t qi, uint32_t ti,
-                                       uint64_t min_match_len, int query_is_rc, uint64_t qstart, uint64_t tstart) {
-  if (!c || !cigar) return SRGPU_E_ARG;
+// Host half of the batched CIGAR walk: RLE string -> run list (count << 3 | op). Adjacent 'M'/'=' ops
+// are merged (they continue one match run, src/seqrush.rs:1214-1218); a missing count is 1 (:1262-1264);
+// any other character is an op that only flushes the run (:1436-1437).
+static void parse_cigar_runs(const char* cg, std::vector<unsigned long long>& runs) {
+  unsigned long long count = 0;
+  const size_t first = runs.size();
+  for (const char* p = cg; *p; ++p) {
+    const char ch = *p;
+    if (ch >= '0' && ch <= '9') {
+      count = count * 10 + (unsigned long long)(ch - '0');
+      continue;
+    }
+    if (count == 0) count = 1;
+    const unsigned op = (ch == 'M' || ch == '=') ? 0u : ch == 'X' ? 1u : ch == 'I' ? 2u : ch == 'D' ? 3u : 4u;
+    if (op == 0u && runs.size() > first && (runs.back() & 7ull) == 0ull) runs.back() += count << 3;
+    else runs.push_back((count << 3) | op);
+    count = 0;
+  }
+}
+
+extern "C" int srgpu_process_alignments(srgpu_ctx* c, srgpu_uf* uf, const srgpu_paf_record* recs, uint64_t n,
+                                        uint64_t min_match_len) {
+  if (!c || (!recs && n)) return SRGPU_E_ARG;
   std::lock_guard<std::mutex> lk(c->mu);
   CK(cudaSetDevice(c->device));
   int rc;
   if ((rc = check_uf(c, uf))) return rc;
-  if (qi >= c->n_seqs || ti >= c->n_seqs) {
-    g_err = "sequence index out of range";
+  if (n == 0) return SRGPU_OK;
+  if (n > 0xfffffff0ull) {
+    g_err = "too many records in one call";
     return SRGPU_E_ARG;
   }
-  const size_t n = strlen(cigar);
-  if ((rc = c->d_cigar_str.ensure(n + 1))) return rc;
-  CK(cudaMemcpyAsync(c->d_cigar_str.p, cigar, n, cudaMemcpyHostToDevice, c->stream));
-  process_alignment_kernel<<<1, 32, 0, c->stream>>>(seq_table(c), c->d_cigar_str.p, (uint32_t)n, qi, ti, min_match_len,
-                                                    query_is_rc, qstart, tstart, uf->parent.p, uf->counters.p);
+  std::vector<PafRecordDev> h(n);
+  std::vector<unsigned long long> runs;
+  for (uint64_t i = 0; i < n; ++i) {
+    const srgpu_paf_record& r = recs[i];
+    if (r.query_idx >= c->n_seqs || r.target_idx >= c->n_seqs || !r.cigar) {
+      g_err = "record " + std::to_string(i) + ": sequence index out of range or missing CIGAR";
+      return SRGPU_E_ARG;
+    }
+    const size_t off = runs.size();
+    parse_cigar_runs(r.cigar, runs);
+    if (runs.size() - off > 0xfffffff0ull) {
+      g_err = "CIGAR with too many operations";
+      return SRGPU_E_ARG;
+    }
+    h[i].q = r.query_idx;
+    h[i].t = r.target_idx;
+    h[i].query_is_rc = r.query_is_rc ? 1u : 0u;
+    h[i].n_runs = (uint32_t)(runs.size() - off);
+    h[i].qstart = r.query_start;
+    h[i].tstart = r.target_start;
+    h[i].run_off = off;
+  }
+  if ((rc = c->d_paf_recs.ensure(n)) || (rc = c->d_paf_runs.ensure(runs.size() + 1))) return rc;
+  CK(cudaMemcpyAsync(c->d_paf_recs.p, h.data(), n * sizeof(PafRecordDev), cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(c->d_paf_runs.p, runs.data(), runs.size() * 8, cudaMemcpyHostToDevice, c->stream));
+  PafArgs a;
+  a.seqs = seq_table(c);
+  a.recs = c->d_paf_recs.p;
+  a.runs = c->d_paf_runs.p;
+  a.n_recs = (uint32_t)n;
+  a.parent = uf->parent.p;
+  a.min_match_len = min_match_len;
+  a.counters = uf->counters.p;
+  paf_walk_kernel<256><<<(unsigned)std::min<uint64_t>(n, (uint64_t)c->n_sm * 8), 256, 0, c->stream>>>(a);
   CK(cudaGetLastError());
-  CK(cudaStreamSynchronize(c->stream));
+  CK(cudaStreamSynchronize(c->stream));  // h / runs are pageable host memory: keep them alive until the copies are done
+  c->stats.kernel_launches++;
+  unsigned long long cnt[2];
+  CK(cudaMemcpy(cnt, uf->counters.p, sizeof cnt, cudaMemcpyDeviceToHost));
+  c->stats.unite_ops = cnt[0];
+  c->stats.unite_links = cnt[1];
   return SRGPU_OK;
+}
+
+extern "C" int srgpu_process_alignment(srgpu_ctx* c, srgpu_uf* uf, const char* cigar, uint32_t qi, uint32_t ti,
+                                       uint64_t min_match_len, int query_is_rc, uint64_t qstart, uint64_t tstart) {
+  if (!c || !cigar) return SRGPU_E_ARG;
+  srgpu_paf_record r;
+  r.query_idx = qi;
+  r.target_idx = ti;
+  r.query_is_rc = query_is_rc;
+  r.reserved = 0;
+  r.query_start = qstart;
+  r.target_start = tstart;
+  r.cigar = cigar;
+  return srgpu_process_alignments(c, uf, &r, 1, min_match_len);
 }
 
 // ---------------------------------------------------------------------------
@@ -1032,6 +1124,33 @@ extern "C" int srgpu_uf_compress(srgpu_uf* u) {
   uf_compress_kernel<<<grid_for(u->capacity, 256, c->n_sm), 256, 0, c->stream>>>(u->parent.p, u->capacity);
   CK(cudaGetLastError());
   CK(cudaStreamSynchronize(c->stream));
+  return SRGPU_OK;
+}
+
+extern "C" int srgpu_uf_compress_async(srgpu_uf* u) {
+  if (!u) return SRGPU_E_ARG;
+  UF_ALIVE(u);
+  srgpu_ctx* c = u->ctx;
+  std::lock_guard<std::mutex> lk(c->mu);
+  CK(cudaSetDevice(c->device));
+  uf_compress_kernel<<<grid_for(u->capacity, 256, c->n_sm), 256, 0, c->stream>>>(u->parent.p, u->capacity);
+  CK(cudaGetLastError());
+  return SRGPU_OK;
+}
+
+extern "C" int srgpu_uf_merge_gathered(srgpu_uf* u, const void* d_gathered, uint64_t n, int world, int my_rank) {
+  if (!u || !d_gathered || world < 1 || my_rank < 0 || my_rank >= world) return SRGPU_E_ARG;
+  UF_ALIVE(u);
+  srgpu_ctx* c = u->ctx;
+  std::lock_guard<std::mutex> lk(c->mu);
+  CK(cudaSetDevice(c->device));
+  if (n != u->capacity) {
+    g_err = "gathered forests must have the capacity of this union-find";
+    return SRGPU_E_ARG;
+  }
+  uf_merge_gathered_kernel<<<grid_for(n, 256, c->n_sm), 256, 0, c->stream>>>(u->parent.p, (const uint32_t*)d_gathered, n,
+                                                                            world, my_rank, u->counters.p);
+  CK(cudaGetLastError());
   return SRGPU_OK;
 }
 

@@ -167,6 +167,7 @@ __global__ void __launch_bounds__(THREADS) orient_kernel(AlignArgs a) {
   cx.tid = threadIdx.x;
   cx.nt = THREADS;
   cx.parity = 0;
+  cx.stage = nullptr;
   int32_t* obuf = a.orient + (size_t)blockIdx.x * a.orient_stride;
   const int lbits = a.seqs.lbits;
   const bool staged = a.smem_seq_words != 0;
@@ -212,7 +213,9 @@ __global__ void __launch_bounds__(THREADS) orient_kernel(AlignArgs a) {
 
 template <int THREADS, int MIN_CTAS>
 __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
-  extern __shared__ __align__(16) uint32_t s_seq[];  // [query strand chosen by orient_kernel | target], smem_seq_words each
+  // dynamic shared memory: [query strand chosen by orient_kernel | target] (smem_seq_words each; absent when the
+  // sequences are read from global memory through L1) followed by the per-warp row staging buffers of the score step
+  extern __shared__ __align__(16) uint32_t s_seq[];
   __shared__ CtaShared sh;
   __shared__ unsigned int s_pair;
   __shared__ unsigned int s_cnt[8];
@@ -222,6 +225,7 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
   cx.tid = threadIdx.x;
   cx.nt = THREADS;
   cx.parity = 0;
+  cx.stage = reinterpret_cast<int32_t*>(s_seq + 2 * (size_t)a.smem_seq_words);
   const size_t b = blockIdx.x;
   PairWorkspace ws;
   ws.ring_f = a.ring + b * a.ring_stride;
@@ -239,7 +243,7 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
   if (staged && threadIdx.x == 0) mbar_init(&s_bar, 1);
 #ifdef WFA_PROFILE
   if (threadIdx.x == 0)
-    for (int i = 0; i < 16; ++i) sh.prof[i] = 0;
+    for (int i = 0; i < 20; ++i) sh.prof[i] = 0;
   const long long prof_start = clock64();
 #endif
   while (true) {
@@ -376,6 +380,8 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
     printf("[prof cta %d] ring steps %llu  total cyc %lld | per step: top-barrier %.0f  setup %.0f  loop %.0f  finish %.0f  "
            "(barrier wait %.0f) | avg width %.0f\n",
            (int)blockIdx.x, pf[0], clock64() - prof_start, pf[1] / n, pf[2] / n, pf[3] / n, pf[4] / n, pf[5] / n, pf[7] / n);
+    printf("[prof cta %d] passes %llu, chunks per pass %.2f, passes with <= 1 chunk per warp %.1f%%\n", (int)blockIdx.x, pf[16],
+           pf[16] ? (double)pf[17] / pf[16] : 0.0, pf[16] ? 100.0 * pf[18] / pf[16] : 0.0);
     printf("[prof cta %d] strand choice %llu cyc (sum of edit distances %llu), BiWFA %llu cyc\n", (int)blockIdx.x, pf[13], pf[15], pf[14]);
     printf("[prof cta %d] warp1 interior chunks %llu: compute %.0f cyc, extend %.0f cyc | warp0 fringe chunks %llu: %.0f cyc\n",
            (int)blockIdx.x, pf[8], pf[9] / (pf[8] ? (double)pf[8] : 1.0), pf[10] / (pf[8] ? (double)pf[8] : 1.0), pf[11],
@@ -457,7 +463,7 @@ struct UnionArgs {
   const uint32_t* todo;  // optional indirection (retry lists)
   uint32_t* parent;
   unsigned long long min_match_len;
-  unsigned long long* counters;  // [0] unite ops, [1] links, [2] validation failures
+  unsigned long long* counters;  // [0] unite ops, [1] links
 };
 
 static constexpr int UNION_TILE = 1024;
@@ -760,6 +766,19 @@ __global__ void uf_merge_kernel(uint32_t* parent, const uint32_t* peer, uint64_t
   }
   if (links) atomicAdd(&counters[1], links);
 }
+// merge of the gathered forests of every rank in ONE pass (gathered = [world][n] compressed parent arrays)
+__global__ void uf_merge_gathered_kernel(uint32_t* parent, const uint32_t* __restrict__ gathered, uint64_t n, int world,
+                                         int me, unsigned long long* counters) {
+  unsigned long long links = 0;
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    for (int r = 0; r < world; ++r) {
+      if (r == me) continue;
+      const uint32_t root = gathered[(uint64_t)r * n + i];
+      if (root != (uint32_t)i && root < n && uf_unite(parent, (uint32_t)i, root)) ++links;
+    }
+  }
+  if (links) atomicAdd(&counters[1], links);
+}
 __global__ void uf_count_kernel(uint32_t* parent, uint64_t total_len, uint32_t* bitmap, unsigned long long* count) {
   // distinct representatives over forward Pos (src/seqrush.rs:341-353): mark each root once
   unsigned long long c = 0;
@@ -785,75 +804,211 @@ __global__ void uf_checksum_kernel(uint32_t* parent, uint64_t n, unsigned long l
   if (c) atomicAdd(sum, c);
 }
 
-// generic CIGAR-string walk (the --paf ingestion path shares process_alignment,
-// src/seqrush.rs:510-609): single thread, per-base re-check of 'M'/'=' like :1267-1358.
-__global__ void process_alignment_kernel(SeqTable seqs, const char* cigar, uint32_t cigar_len, uint32_t qi, uint32_t ti,
-                                         unsigned long long min_match_len, int query_is_rc, unsigned long long qstart,
-                                         unsigned long long tstart, uint32_t* parent, unsigned long long* counters) {
-  if (threadIdx.x != 0 || blockIdx.x != 0) return;
-  const uint8_t* q = seqs.fwd + seqs.byte_off[qi];
-  const uint8_t* t = seqs.fwd + seqs.byte_off[ti];
-  const uint32_t qlen = seqs.len[qi], tlen = seqs.len[ti];
-  const uint64_t qoff = seqs.pos_off[qi], toff = seqs.pos_off[ti];
-  unsigned long long p1 = qstart, p2 = tstart, count = 0;
-  bool in_run = false;
-  unsigned long long rs1 = 0, rs2 = 0, rl = 0;
+// ---------------------------------------------------------------------------
+// Batched CIGAR walk for alignments that come from elsewhere (--paf, src/seqrush.rs:510-609, and
+// any caller of process_alignment, :1134-1481). One CTA per record walks a run list the host parsed
+// from the RLE string: op 0 = 'M' or '=' (re-checked base by base like the reference, :1267-1358;
+// adjacent M/= ops are merged by the host, they continue one match run, :1214-1218), 1 = 'X',
+// 2 = 'I' (query += n), 3 = 'D' (target += n), 4 = any other letter (flushes the run, moves
+// nothing, :1436-1437). Tiles of runs are prefix-summed like in union_kernel; the bases of the
+// match-type runs of a tile are then flattened in 32-base words over the threads. A thread compares
+// its word's bases, and a base is united when the maximal stretch of equal bases around it (inside
+// its run: every other op flushes) is at least min_match_len long; only stretches that touch a word
+// edge look at the neighbouring bases, at most min_match_len of them.
+// ---------------------------------------------------------------------------
+struct PafRecordDev {
+  uint32_t q, t;
+  uint32_t query_is_rc, n_runs;
+  unsigned long long qstart, tstart;
+  unsigned long long run_off;
+};
+struct PafArgs {
+  SeqTable seqs;
+  const PafRecordDev* recs;
+  const unsigned long long* runs;  // (count << 3) | op
+  uint32_t n_recs;
+  uint32_t* parent;
+  unsigned long long min_match_len;
+  unsigned long long* counters;  // [0] unite ops, [1] links
+};
+
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS) paf_walk_kernel(PafArgs a) {
+  constexpr int TILE = 1024, PER = TILE / THREADS;
+  __shared__ unsigned long long s_qpos[TILE], s_tpos[TILE];
+  __shared__ uint32_t s_len[TILE];       // bases of a match-type run that lie inside both sequences (0 for other ops)
+  __shared__ uint32_t s_wcum[TILE + 1];  // exclusive prefix of 32-base words
+  __shared__ unsigned long long s_scan[2][THREADS];
+  __shared__ uint32_t s_scanw[THREADS];
+  __shared__ unsigned long long s_carry[2];
   unsigned long long ops = 0, links = 0;
-  auto flush = [&]() {
-    if (in_run && rl >= min_match_len) {
-      for (unsigned long long j = 0; j < rl; ++j) {
-        const uint32_t x = query_is_rc ? (uint32_t)(2 * (qoff + qlen - 1 - (rs1 + j)) + 1) : (uint32_t)(2 * (qoff + rs1 + j));
-        const uint32_t y = (uint32_t)(2 * (toff + rs2 + j));
-        ++ops;
-        if (uf_unite(parent, x, y)) ++links;
-      }
+  for (uint32_t ri = blockIdx.x; ri < a.n_recs; ri += gridDim.x) {
+    const PafRecordDev rec = a.recs[ri];
+    const uint8_t* q = a.seqs.fwd + a.seqs.byte_off[rec.q];
+    const uint8_t* t = a.seqs.fwd + a.seqs.byte_off[rec.t];
+    const unsigned long long qlen = a.seqs.len[rec.q], tlen = a.seqs.len[rec.t];
+    const unsigned long long qoff = a.seqs.pos_off[rec.q], toff = a.seqs.pos_off[rec.t];
+    const bool rc = rec.query_is_rc != 0;
+    const unsigned long long k = a.min_match_len;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      s_carry[0] = rec.qstart;
+      s_carry[1] = rec.tstart;
     }
-    in_run = false;
-    rl = 0;
-  };
-  for (uint32_t ci = 0; ci < cigar_len; ++ci) {
-    const char ch = cigar[ci];
-    if (ch >= '0' && ch <= '9') {
-      count = count * 10 + (unsigned long long)(ch - '0');
-      continue;
-    }
-    if (count == 0) count = 1;
-    if (ch == 'M' || ch == '=') {
-      for (unsigned long long k = 0; k < count; ++k) {
-        if (p1 + k < qlen && p2 + k < tlen) {
-          const bool eq = seqrush_query_base(q, qlen, (uint32_t)(p1 + k), query_is_rc != 0) == t[p2 + k];
-          if (eq) {
-            if (!in_run) {
-              in_run = true;
-              rs1 = p1 + k;
-              rs2 = p2 + k;
-              rl = 1;
-            } else {
-              ++rl;
-            }
-          } else {
-            flush();
-          }
+    __syncthreads();
+    for (uint32_t tile0 = 0; tile0 < rec.n_runs; tile0 += TILE) {
+      const uint32_t nt = min((uint32_t)TILE, rec.n_runs - tile0);
+      unsigned long long runs[PER];
+      unsigned long long dq = 0, dt = 0;
+#pragma unroll
+      for (int j = 0; j < PER; ++j) {
+        const uint32_t i = threadIdx.x * PER + j;
+        const unsigned long long run = (i < nt) ? a.runs[rec.run_off + tile0 + i] : 4ull;
+        runs[j] = run;
+        const unsigned op = (unsigned)(run & 7ull);
+        const unsigned long long len = run >> 3;
+        if (op <= 1u) {
+          dq += len;
+          dt += len;
+        } else if (op == 2u) {
+          dq += len;
+        } else if (op == 3u) {
+          dt += len;
         }
       }
-      p1 += count;
-      p2 += count;
-    } else {
-      flush();
-      if (ch == 'X') {
-        p1 += count;
-        p2 += count;
-      } else if (ch == 'I') {
-        p1 += count;  // SAM convention here (after cigar_bytes_to_string's swap): I consumes the query
-      } else if (ch == 'D') {
-        p2 += count;
+      s_scan[0][threadIdx.x] = dq;
+      s_scan[1][threadIdx.x] = dt;
+      __syncthreads();
+      for (int ofs = 1; ofs < THREADS; ofs <<= 1) {
+        unsigned long long v0 = 0, v1 = 0;
+        if ((int)threadIdx.x >= ofs) {
+          v0 = s_scan[0][threadIdx.x - ofs];
+          v1 = s_scan[1][threadIdx.x - ofs];
+        }
+        __syncthreads();
+        s_scan[0][threadIdx.x] += v0;
+        s_scan[1][threadIdx.x] += v1;
+        __syncthreads();
       }
+      unsigned long long q0 = s_carry[0] + s_scan[0][threadIdx.x] - dq;
+      unsigned long long t0 = s_carry[1] + s_scan[1][threadIdx.x] - dt;
+      const unsigned long long tq = s_scan[0][THREADS - 1], tt = s_scan[1][THREADS - 1];
+      uint32_t dw = 0;
+#pragma unroll
+      for (int j = 0; j < PER; ++j) {
+        const uint32_t i = threadIdx.x * PER + j;
+        const unsigned op = (unsigned)(runs[j] & 7ull);
+        const unsigned long long len = runs[j] >> 3;
+        s_qpos[i] = q0;
+        s_tpos[i] = t0;
+        uint32_t inside = 0;
+        if (op == 0u && q0 < qlen && t0 < tlen) {
+          // positions beyond either sequence are skipped without ending the run (:1268); they can
+          // only be the tail of a run, so clipping the run is the same thing
+          unsigned long long m = len;
+          if (qlen - q0 < m) m = qlen - q0;
+          if (tlen - t0 < m) m = tlen - t0;
+          inside = (uint32_t)m;
+        }
+        s_len[i] = inside;
+        dw += (inside + 31u) >> 5;
+        if (op <= 1u) {
+          q0 += len;
+          t0 += len;
+        } else if (op == 2u) {
+          q0 += len;
+        } else if (op == 3u) {
+          t0 += len;
+        }
+      }
+      s_scanw[threadIdx.x] = dw;
+      __syncthreads();
+      for (int ofs = 1; ofs < THREADS; ofs <<= 1) {
+        uint32_t v = 0;
+        if ((int)threadIdx.x >= ofs) v = s_scanw[threadIdx.x - ofs];
+        __syncthreads();
+        s_scanw[threadIdx.x] += v;
+        __syncthreads();
+      }
+      {
+        uint32_t w0 = s_scanw[threadIdx.x] - dw;
+#pragma unroll
+        for (int j = 0; j < PER; ++j) {
+          const uint32_t i = threadIdx.x * PER + j;
+          s_wcum[i] = w0;
+          w0 += (s_len[i] + 31u) >> 5;
+        }
+        if (threadIdx.x == THREADS - 1) s_wcum[TILE] = s_scanw[THREADS - 1];
+      }
+      __syncthreads();
+      const uint32_t words = s_wcum[TILE];
+      uint32_t lo = 0;
+      for (uint32_t w = threadIdx.x; w < words; w += THREADS) {
+        while (s_wcum[lo + 1] <= w) ++lo;  // w only grows: linear advance
+        const uint32_t rl = s_len[lo];
+        const uint32_t b0 = (w - s_wcum[lo]) << 5;
+        const uint32_t nb = min(32u, rl - b0);
+        const unsigned long long p1 = s_qpos[lo], p2 = s_tpos[lo];
+        auto eq_at = [&](uint32_t i) -> bool {
+          return seqrush_query_base(q, (uint32_t)qlen, (uint32_t)(p1 + i), rc) == t[p2 + i];
+        };
+        uint32_t mask = 0;
+        for (uint32_t i = 0; i < nb; ++i) mask |= (eq_at(b0 + i) ? 1u : 0u) << i;
+        if (!mask) continue;
+        uint32_t take = mask;
+        if (k > 1) {
+          // stretches of equal bases inside the word; the first / last may continue in the neighbours
+          take = 0;
+          uint32_t m = mask;
+          while (m) {
+            const uint32_t s0 = (uint32_t)__ffs((int)m) - 1u;
+            uint32_t e0 = s0;  // exclusive end
+            while (e0 < nb && ((mask >> e0) & 1u)) ++e0;
+            unsigned long long ln = e0 - s0;
+            if (ln < k && s0 == 0) {
+              uint32_t i = b0;
+              while (ln < k && i > 0 && eq_at(i - 1)) {
+                --i;
+                ++ln;
+              }
+            }
+            if (ln < k && e0 == nb) {
+              uint32_t i = b0 + nb;
+              while (ln < k && i < rl && eq_at(i)) {
+                ++i;
+                ++ln;
+              }
+            }
+            const uint32_t bits = (e0 - s0 >= 32u) ? 0xffffffffu : (((1u << (e0 - s0)) - 1u) << s0);
+            if (ln >= k) take |= bits;
+            m &= ~bits;
+          }
+        }
+        while (take) {
+          const uint32_t i = b0 + (uint32_t)__ffs((int)take) - 1u;
+          take &= take - 1u;
+          const unsigned long long x = rc ? 2ull * (qoff + qlen - 1ull - (p1 + i)) + 1ull : 2ull * (qoff + p1 + i);
+          const unsigned long long y = 2ull * (toff + p2 + i);
+          ++ops;
+          if (uf_unite(a.parent, (uint32_t)x, (uint32_t)y)) ++links;
+        }
+      }
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        s_carry[0] += tq;
+        s_carry[1] += tt;
+      }
+      __syncthreads();
     }
-    count = 0;
   }
-  flush();
-  atomicAdd(&counters[0], ops);
-  atomicAdd(&counters[1], links);
+  ops = __reduce_add_sync(0xffffffffu, (unsigned)(ops & 0xffffffffu)) +
+        ((unsigned long long)__reduce_add_sync(0xffffffffu, (unsigned)(ops >> 32)) << 32);
+  links = __reduce_add_sync(0xffffffffu, (unsigned)(links & 0xffffffffu)) +
+          ((unsigned long long)__reduce_add_sync(0xffffffffu, (unsigned)(links >> 32)) << 32);
+  if ((threadIdx.x & 31) == 0) {
+    if (ops) atomicAdd(&a.counters[0], ops);
+    if (links) atomicAdd(&a.counters[1], links);
+  }
 }
 
 }  // namespace srb

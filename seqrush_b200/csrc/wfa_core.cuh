@@ -172,7 +172,7 @@ struct CtaShared {
   unsigned long long cells;   // BiWFA cells: one diagonal at one score, all five components
   unsigned long long ocells;  // orientation (unit-cost) cells
 #ifdef WFA_PROFILE
-  unsigned long long prof[16];  // cycle counters of thread 0 (development only)
+  unsigned long long prof[20];  // cycle counters of thread 0 (development only)
 #endif
 };
 
@@ -180,7 +180,14 @@ struct Ctx {
   CtaShared* sh;
   int tid, nt;
   int parity;
+  int32_t* stage;  // device: shared-memory staging of the source-row slices of a chunk (per warp 2 x STAGE_INTS)
 };
+
+// Staged source rows of one chunk: seven rows (o1, o2, i1, i2, d1, d2, mis in the order of DS_O1..DS_MIS),
+// each the 128 diagonals of the chunk plus four on either side (the k-1 / k+1 neighbours of the
+// chunk's edge cells), as 16-byte segments.
+static constexpr int STAGE_ROW = 32 * 4 + 8;
+static constexpr int STAGE_INTS = 7 * STAGE_ROW;
 
 #if WFA_DEVICE
 WFA_FN void cta_sync() { __syncthreads(); }
@@ -803,6 +810,19 @@ WFA_FN void st4(int32_t* p, int32_t a, int32_t b, int32_t c, int32_t e) {
 #endif
 }
 
+#if WFA_DEVICE
+// 16-byte asynchronous copy global -> shared, L2 only (ring rows have no reuse in L1)
+WFA_FN void cp_async16(int32_t* dst_smem, const int32_t* src_gmem) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src_gmem)
+               : "memory");
+}
+WFA_FN void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+WFA_FN void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+#endif
+
 // first/last valid diagonal of one component inside a chunk where lane l holds diagonals kb+4l+j
 struct Span4 {  // LANE-local first/last valid diagonal of one component; reduced over the warp when flushed
   int mn, mx;
@@ -1058,7 +1078,13 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
   };
   // Chunks of both directions are claimed from one shared counter; inside a direction the two
   // fringe chunks (masked reads, per-cell trims: ~1.5x an interior chunk) go first.
-  while (true) {
+  // The seven source-row slices of a chunk are staged in shared memory by asynchronous 16-byte
+  // copies, double-buffered per warp: a warp claims its NEXT chunk and starts that chunk's copies
+  // before it computes the current one, so the global-memory latency of the row reads (38 % of all
+  // warp stall samples when the rows were read straight into registers: profiles/r02b_*) is covered
+  // by one chunk of compute instead of being waited for. The copies cost no registers.
+  int n_dir = -1, n_kb = 0;
+  auto claim_next = [&]() {
     int claim = 0;
 #if WFA_DEVICE
     if (lane == 0) claim = atomicAdd(&cx.sh->chunk_ctr, 1);
@@ -1066,8 +1092,49 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
 #else
     claim = cx.sh->chunk_ctr++;
 #endif
-    const bool done = claim >= nch_all;
-    const int dir = done ? -1 : (claim >= nch0 ? 1 : 0);
+    if (claim >= nch_all) {
+      n_dir = -1;
+      n_kb = 0;
+      return;
+    }
+    n_dir = claim >= nch0 ? 1 : 0;
+    const volatile int* sn = cx.sh->ds[n_dir];
+    const int cl = claim - (n_dir ? nch0 : 0), nchunks = sn[DS_NCH];
+    const int ci = cl == 0 ? 0 : (cl == 1 ? nchunks - 1 : cl - 1);
+    n_kb = sn[DS_LOAL] + ci * CH;
+  };
+#if WFA_DEVICE
+  int32_t* const wstage = cx.stage + warp * (2 * STAGE_INTS);
+  int stage = 0;
+  // copies of the slices [kb-4, kb+132) of the seven source rows of chunk (pdir, pkb) into buffer pst.
+  // Segments that start beyond hi+4 are not read (they would leave the row allocation, which keeps
+  // 8 diagonals of slack); whatever an unread segment holds is outside every source wavefront and is
+  // masked (fringe chunk) or belongs to lanes that neither compute a valid cell nor store.
+  auto prefetch = [&](int pdir, int pkb, int pst) {
+    if (pdir >= 0) {
+      const volatile int* sp = cx.sh->ds[pdir];
+      const int phi = sp[DS_HI] + 4;
+      int32_t* sb = wstage + pst * STAGE_INTS;
+      const int ks = pkb - 4 + 4 * lane;   // segment `lane`
+      const int ks2 = ks + 128;            // segments 32, 33 (lanes 0 and 1)
+      const bool ok0 = ks <= phi, ok1 = lane < 2 && ks2 <= phi;
+#pragma unroll
+      for (int r = 0; r < 7; ++r) {
+        const int off = sp[DS_O1 + r];
+        if (ok0) cp_async16(sb + r * STAGE_ROW + 4 * lane, ring + (off + ks));
+        if (ok1) cp_async16(sb + r * STAGE_ROW + 128 + 4 * lane, ring + (off + ks2));
+      }
+    }
+    cp_async_commit();
+  };
+#endif
+  claim_next();
+#if WFA_DEVICE
+  prefetch(n_dir, n_kb, 0);
+#endif
+  while (true) {
+    const int dir = n_dir, kb = n_kb;
+    const bool done = dir < 0;
     if (dir != acc_dir) {
       if (acc_dir >= 0) flush(acc_dir);  // the only flush site: a direction change or the end of the pool
       if (done) break;
@@ -1080,23 +1147,37 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
       acc_dir = dir;
     }
     if (done) break;  // a warp that claimed nothing has acc_dir == dir == -1
+#if WFA_DEVICE
+    __syncwarp();  // every lane has finished reading the other buffer (previous chunk)
+#endif
+    claim_next();
+#if WFA_DEVICE
+    prefetch(n_dir, n_kb, stage ^ 1);
+    cp_async_wait<1>();  // this chunk's copies have landed (the group just committed may still fly)
+    __syncwarp();
+#endif
     const volatile int* su = cx.sh->ds[dir];
-    const int cl = claim - (dir ? nch0 : 0), nchunks = su[DS_NCH];
-    const int ci = cl == 0 ? 0 : (cl == 1 ? nchunks - 1 : cl - 1);
-    const int lo = su[DS_LO], hi = su[DS_HI], lo_al = su[DS_LOAL];
+    const int lo = su[DS_LO], hi = su[DS_HI];
     const int fl = su[DS_FLAGS];
     const bool a_i1 = fl & 1, a_i2 = fl & 2, a_d1 = fl & 4, a_d2 = fl & 8;
     const int dp0 = su[DS_P0], dt0 = su[DS_T0], drev = su[DS_REV], dcend = su[DS_CEND];
-    const int kb = lo_al + ci * CH;
     const int k0 = kb + 4 * lane;
     int32_t ins1[4], ins2[4], del1[4], del2[4], mx[4];
     bool vm[4];
     PROF_T(tc0);
-    // 128-bit reads of the seven source rows (always inside the row allocation: rows keep >= 8
-    // diagonals of slack beyond [lo, hi]); neighbours k0-1 / k0+4 by shuffle, chunk edges by a load
-    // lanes of the last chunk that lie wholly beyond hi neither load nor store (they would leave
-    // the row); kq is a safe stand-in address for them
+    // lanes of the last chunk that lie wholly beyond hi do not store (they would leave the row)
     const bool lane_act = k0 <= hi;
+#if WFA_DEVICE
+    // own four cells of every row with one 128-bit shared-memory read, the k0-1 / k0+4 neighbours
+    // with scalar reads of the same staged slice
+    const int32_t* sb = wstage + stage * STAGE_INTS + 4 + 4 * lane;
+    stage ^= 1;
+    I4 vo1 = ld4(sb), vo2 = ld4(sb + STAGE_ROW), vi1 = ld4(sb + 2 * STAGE_ROW), vi2 = ld4(sb + 3 * STAGE_ROW);
+    I4 vd1 = ld4(sb + 4 * STAGE_ROW), vd2 = ld4(sb + 5 * STAGE_ROW), vmis = ld4(sb + 6 * STAGE_ROW);
+    int32_t o1L = sb[-1], o2L = sb[STAGE_ROW - 1], i1L = sb[2 * STAGE_ROW - 1], i2L = sb[3 * STAGE_ROW - 1];
+    int32_t o1R = sb[4], o2R = sb[STAGE_ROW + 4], d1R = sb[4 * STAGE_ROW + 4], d2R = sb[5 * STAGE_ROW + 4];
+#else
+    const int lo_al = su[DS_LOAL];
     const int kq = lane_act ? k0 : lo_al;
     const int32_t* const r_o1 = ring + (su[DS_O1] + kq);
     const int32_t* const r_o2 = ring + (su[DS_O2] + kq);
@@ -1106,35 +1187,10 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
     const int32_t* const r_d2 = ring + (su[DS_D2] + kq);
     I4 vo1 = ld4(r_o1), vo2 = ld4(r_o2), vi1 = ld4(r_i1), vi2 = ld4(r_i2);
     I4 vd1 = ld4(r_d1), vd2 = ld4(r_d2), vmis = ld4(ring + (su[DS_MIS] + kq));
-    // chunk-edge neighbours: issued together with the row reads (before the shuffles wait for
-    // those), so a chunk pays one global-memory latency, not two
-    int32_t eL0 = 0, eL1 = 0, eL2 = 0, eL3 = 0, eR0 = 0, eR1 = 0, eR2 = 0, eR3 = 0;
-    if (lane == 0) {
-      eL0 = r_o1[-1];
-      eL1 = r_o2[-1];
-      eL2 = r_i1[-1];
-      eL3 = r_i2[-1];
-    }
-    if (lane == LANES - 1) {
-      eR0 = r_o1[4];
-      eR1 = r_o2[4];
-      eR2 = r_d1[4];
-      eR3 = r_d2[4];
-    }
-    int32_t o1L = shfl_up1(vo1.w), o2L = shfl_up1(vo2.w), i1L = shfl_up1(vi1.w), i2L = shfl_up1(vi2.w);
-    int32_t o1R = shfl_down1(vo1.x), o2R = shfl_down1(vo2.x), d1R = shfl_down1(vd1.x), d2R = shfl_down1(vd2.x);
-    if (lane == 0) {
-      o1L = eL0;
-      o2L = eL1;
-      i1L = eL2;
-      i2L = eL3;
-    }
-    if (lane == LANES - 1) {
-      o1R = eR0;
-      o2R = eR1;
-      d1R = eR2;
-      d2R = eR3;
-    }
+    // host emulation: one "lane", so the k0-1 / k0+4 neighbours are plain reads
+    int32_t o1L = r_o1[-1], o2L = r_o2[-1], i1L = r_i1[-1], i2L = r_i2[-1];
+    int32_t o1R = r_o1[4], o2R = r_o2[4], d1R = r_d1[4], d2R = r_d2[4];
+#endif
     const bool interior = kb >= su[DS_INLO] && kb + CH - 1 <= su[DS_INHI];  // warp-uniform
     if (!interior) {
       // fringe chunk: whatever lies outside its source wavefront reads as NULL
@@ -1374,6 +1430,9 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
     pf[3] += t3 - t2;  // chunk loop (warp 0)
     pf[4] += t6 - t3;  // closing barrier, publish, end test
     pf[7] += (unsigned long long)(cx.sh->ds[0][DS_NCH] ? cx.sh->ds[0][DS_WIDTH] : 0) + (cx.sh->ds[1][DS_NCH] ? cx.sh->ds[1][DS_WIDTH] : 0);
+    pf[16] += 1;  // passes
+    pf[17] += (unsigned long long)nch_all;
+    pf[18] += (nch_all <= nwarps) ? 1 : 0;
   }
 #endif
   return out;

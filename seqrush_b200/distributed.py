@@ -12,7 +12,8 @@ def shard_pairs(pairs: np.ndarray, rank: int, world: int) -> np.ndarray:
 
 
 def merge_forests(local_roots, world: int, dist, unite_with_peer):
-    """local_roots: tensor of this rank's compressed parent array (parent[p] == find(p)).
+    """Backend-agnostic form of the exchange (the gloo CPU tests drive it with a host union-find).
+    local_roots: tensor of this rank's compressed parent array (parent[p] == find(p)).
     Gathers every rank's array and calls unite_with_peer(peer_roots_tensor) for each other rank."""
     import torch
 
@@ -25,22 +26,41 @@ def merge_forests(local_roots, world: int, dist, unite_with_peer):
     return gathered
 
 
-def merge_device_union_finds(uf, dist):
-    """NCCL path: uf is a seqrush_b200.BidirectedUnionFind."""
+_gather_buf = {}
+
+
+def merge_device_union_finds(uf, dist, timings=None):
+    """NCCL path: uf is a seqrush_b200.BidirectedUnionFind. Everything is ordered on the context's
+    stream -- compress, ONE all_gather_into_tensor of the compressed parent arrays into a [world, n]
+    buffer, ONE merge pass over all peers, compress -- with no host synchronisation: the collective
+    is issued with the context's stream current, so NCCL waits for the compress kernel and the merge
+    kernel waits for NCCL through stream events. `timings` (optional dict) receives CUDA events."""
     import torch
 
-    uf.compress()
-    t = uf.as_tensor()
     world = dist.get_world_size()
     if world == 1:
+        uf.compress_async()
         return
-    # the library launches on the context's own stream, NCCL on torch's: order them explicitly
-    # (compress -> all_gather -> merge), once per step
-    uf.ctx.synchronize()
-
-    def unite_with_peer(peer):
-        torch.cuda.current_stream(peer.device).synchronize()
-        uf.merge_roots(peer.data_ptr(), peer.numel())
-
-    merge_forests(t, world, dist, unite_with_peer)
-    uf.compress()
+    dev = torch.device("cuda", uf.ctx.device)
+    stream = torch.cuda.ExternalStream(uf.ctx.stream_ptr(), device=dev)
+    n = int(uf.capacity)
+    key = (uf.ctx.device, world, n)
+    buf = _gather_buf.get(key)
+    if buf is None:
+        _gather_buf.clear()
+        buf = _gather_buf[key] = torch.empty((world, n), dtype=torch.int32, device=dev)
+    with torch.cuda.stream(stream):
+        if timings is not None:
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+            ev[0].record(stream)
+        uf.compress_async()
+        t = uf.as_tensor()
+        dist.all_gather_into_tensor(buf.view(-1), t)
+        if timings is not None:
+            ev[1].record(stream)
+        uf.merge_gathered(buf.data_ptr(), world, dist.get_rank())
+        uf.compress_async()
+        if timings is not None:
+            ev[2].record(stream)
+            timings["events"] = ev
+            timings["gathered_bytes"] = int(buf.numel() * 4)

@@ -139,14 +139,23 @@ class SeqRush:
                                                       seq2_idx, min_match_len, int(bool(query_is_rc)), query_start,
                                                       target_start))
 
-    def align_and_unite_from_paf(self, paf_path: str, args: Args = None) -> int:  # :510-609
+    def process_alignments(self, records, min_match_len: int):
+        """Batched process_alignment: records = iterable of (cigar, seq1_idx, seq2_idx, query_is_rc,
+        query_start, target_start); one multi-CTA launch walks them all (srgpu_process_alignments)."""
+        records = list(records)
+        arr = (_lib.PafRecord * len(records))()
+        for i, (cigar, qi, ti, rc, qs, ts) in enumerate(records):
+            arr[i] = _lib.PafRecord(qi, ti, int(bool(rc)), 0, qs, ts, cigar.encode())
+        _lib.check(_lib.lib().srgpu_process_alignments(self.ctx._h, self.union_find._h, arr, len(records), min_match_len))
+
+    def align_and_unite_from_paf(self, paf_path: str, args: Args = None, batch: int = 65536) -> int:  # :510-609
         """Unite from the alignments of a PAF file (ids looked up by name, unknown names and short lines
-        skipped with a warning, strand "-" = query reverse-complemented); every CIGAR is walked on the
-        device by srgpu_process_alignment. Returns the number of alignments processed."""
+        skipped with a warning, strand "-" = query reverse-complemented); the CIGARs are walked on the
+        device, `batch` records per launch. Returns the number of alignments processed."""
         import sys
         args = args or Args()
         idx = {s.id: i for i, s in enumerate(self.sequences)}
-        n = 0
+        n, pending = 0, []
         with open(paf_path, "r") as f:
             for line in f:
                 rec = parse_paf_line(line)
@@ -158,25 +167,29 @@ class SeqRush:
                 if qn not in idx or tn not in idx:
                     print("Warning: Unknown sequence name(s) in PAF: %s or %s" % (qn, tn), file=sys.stderr)
                     continue
-                self.process_alignment(cigar, idx[qn], idx[tn], args.min_match_length, strand == "-", qs, ts)
+                pending.append((cigar, idx[qn], idx[tn], strand == "-", qs, ts))
                 n += 1
+                if len(pending) >= batch:
+                    self.process_alignments(pending, args.min_match_length)
+                    pending = []
+        if pending:
+            self.process_alignments(pending, args.min_match_length)
         return n
 
     def _align_write_paf_and_unite(self, args: Args, pairs=None, batch: int = 1024):
         """--output-alignments (:676-716). The reference aligns every pair twice (once for the PAF, once
-        for the graph); here ONE pass over the pair list yields the CIGARs, which go to the file and
-        through the device CIGAR walk. Records are written in pair order."""
-        from .allwave import AllPairIterator, Sequence as AwSequence, alignment_to_paf, cigar_bytes_to_string
+        for the graph); here ONE pass over the pair list yields the CIGARs, which go to the file while
+        the same pass unites on the device from the run-length CIGARs (srgpu_align_pairs_and_unite).
+        Records are written in pair order."""
+        from .allwave import AllPairIterator, Sequence as AwSequence, alignment_to_paf
         aw = [AwSequence(s.id, s.data) for s in self.sequences]
         it = AllPairIterator.with_options(aw, parse_scores(args.scores), False, False, None,
                                           pairs=self.all_pairs() if pairs is None else pairs, ctx=self.ctx)
         it._uploaded = True  # the context already holds these sequences (SeqRush.__init__)
         with open(args.output_alignments, "w") as f:
-            for rs in it._batches(True, batch):
+            for rs in it._batches(True, batch, unite_into=self.union_find, min_match_len=args.min_match_length):
                 for r in rs:
                     f.write(alignment_to_paf(r, aw) + "\n")
-                    self.process_alignment(cigar_bytes_to_string(r.cigar_bytes), r.query_idx, r.target_idx,
-                                           args.min_match_length, r.is_reverse, 0, 0)
         return self.ctx.stats()
 
     STABILITY_THRESHOLD = 10  # :1038

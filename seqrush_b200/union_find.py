@@ -92,6 +92,13 @@ class BidirectedUnionFind:
     def compress(self):
         _lib.check(_lib.lib().srgpu_uf_compress(self._h))
 
+    def compress_async(self):
+        _lib.check(_lib.lib().srgpu_uf_compress_async(self._h))
+
+    def merge_gathered(self, d_gathered_ptr: int, world: int, my_rank: int):
+        """One pass over the [world][capacity] gathered parent arrays (stream-ordered, no host sync)."""
+        _lib.check(_lib.lib().srgpu_uf_merge_gathered(self._h, d_gathered_ptr, self.capacity, world, my_rank))
+
     def device_ptr(self) -> int:
         return _lib.lib().srgpu_uf_device_ptr(self._h)
 

@@ -228,6 +228,54 @@ def test_process_alignment_paf_path(s, oracle):
         ctx.close()
 
 
+def test_process_alignments_batched(s, oracle):
+    """srgpu_process_alignments: many records in one launch against the restated process_alignment
+    (src/seqrush.rs:1134-1481). 'M' runs that hide mismatches (stretches shorter / longer than
+    min_match_len, across 32-base word edges), adjacent '='/'M' ops continuing one run, ops that only
+    flush ('N', 'S'), a missing count, an 'M' that runs past the end of a sequence, RC queries with
+    IUPAC bytes, and PAF start coordinates."""
+    import _oracle
+    from seqrush_b200 import synth
+    rng = np.random.default_rng(99)
+    acgt = np.frombuffer(b"ACGT", dtype=np.uint8)
+    anc = acgt[rng.integers(0, 4, size=6000)]
+    a = synth.mutate(rng, anc, 0.03)
+    b = synth.mutate(rng, anc, 0.03)
+    c = synth.revcomp(synth.mutate(rng, anc, 0.02)).copy()
+    c[100:104] = np.frombuffer(b"RYKM", dtype=np.uint8)
+    seqs = [a.tobytes(), b.tobytes(), c.tobytes(), b"ACGTACGTAC", b"ACGTTCGTAC"]
+    n1 = min(len(seqs[0]), len(seqs[1]))
+    recs = [
+        ("%dM" % n1, 0, 1, False, 0, 0),                       # one long 'M' hiding every mismatch and indel shift
+        ("%dM" % (n1 - 50), 1, 0, False, 7, 3),                # starts from PAF coordinates
+        ("2000=1000M5X3I2D%dM" % 900, 0, 1, False, 0, 0),      # '=' then 'M' continue one run; X/I/D flush
+        ("100M1N100M2S50=H10M", 0, 1, False, 10, 10),          # letters that only flush; 'H' with a missing count
+        ("%dM" % (len(seqs[0]) + 500), 0, 1, False, 0, 0),     # runs past both ends: skipped, not an error
+        ("%dM" % min(len(seqs[2]), len(seqs[1])), 2, 1, True, 0, 0),  # RC query with IUPAC bytes (kept by seqrush's RC)
+        ("4=1X5=", 3, 4, False, 0, 0),
+        ("M", 3, 4, False, 2, 2),                              # count 0 -> 1
+        ("", 3, 4, False, 0, 0),                               # no cg:Z: tag
+        ("31M1X1M1X33M1X64M", 0, 0, False, 0, 0),              # self record: word-edge stretches
+    ]
+    res = _align(s, [seqs[0], seqs[1]], [(0, 1)])
+    recs.append((s.cigar_bytes_to_string(res[0].cigar_bytes), 0, 1, False, 0, 0))  # a real alignment
+    lens = [len(x) for x in seqs]
+    offs = np.concatenate(([0], np.cumsum(lens)))[:-1]
+    tot = int(sum(lens))
+    for k in (0, 1, 2, 5, 33, 100, 5000):
+        ctx = s.Context(0)
+        sr = s.SeqRush([s.Sequence("s%d" % i, d) for i, d in enumerate(seqs)], ctx=ctx)
+        sr.union_find.close()
+        sr.union_find = s.BidirectedUnionFind(sr.total_length, ctx)
+        sr.process_alignments(recs, k)
+        ouf = _oracle.OracleUF(tot)
+        for cigar, qi, ti, rc, qs, ts in recs:
+            ouf.process_alignment(cigar, seqs[qi], int(offs[qi]), seqs[ti], int(offs[ti]), k, rc, qs, ts)
+        assert ctx.stats()["unite_ops"] == ouf.unite_calls(), k
+        assert np.array_equal(sr.union_find.roots(0, 2 * tot), ouf.canonical(2 * tot)), k
+        ctx.close()
+
+
 def test_properties_at_bench_scale(s):
     """Size-independent properties on a slice of BASELINE.json configs[1] (100 x 50 kb, 1 %): the
     partition does not depend on pair order or launch configuration, re-running is idempotent, CIGARs
@@ -300,7 +348,9 @@ def test_paf_out_and_back_in(s, tmp_path):
         lines = open(paf).read().splitlines()
         assert len(lines) == len(ids) ** 2
         f = lines[1].split("\t")
-        assert len(f) == 13 and f[0] == ids[0] and f[5] == ids[1] and f[12].startswith("cg:Z:") and f[4] in "+-"
+        assert len(f) == 14 and f[0] == ids[0] and f[5] == ids[1] and f[4] in "+-"
+        assert f[12].startswith("gi:f:") and f[13].startswith("cg:Z:")  # allwave/src/lib.rs:95-111
+        assert int(f[10]) == max(int(f[3]) - int(f[2]), int(f[8]) - int(f[7]))
         assert any(l.split("\t")[4] == "-" for l in lines)
         with open(paf, "a") as fh:  # lines the reference skips: empty, short, unknown name
             fh.write("\n" + "x\t1\t0\n" + lines[1].replace(ids[0], "nobody") + "\n")

@@ -35,14 +35,30 @@ def test_allwave_helpers():
 
 
 def test_paf_line():
-    """allwave/src/lib.rs:71-112."""
-    seqs = [s.AllwaveSequence("q", b"ACGTACGT"), s.AllwaveSequence("t", b"ACGTTCGT")]
+    """allwave/src/lib.rs:71-112. Expected lines are written out from the reference's format string
+    "{}\t{}\t{}\t{}\t{}\t{}\t{}\t{}\t{}\t{}\t{}\t{}\tgi:f:{:.6}\tcg:Z:{}" with
+    block_len = max(query_end - query_start, target_end - target_start) and identity =
+    num_matches / alignment_length (0.0 when alignment_length == 0), not from the repo's own reader."""
+    seqs = [s.AllwaveSequence("q", b"ACGTACGT"), s.AllwaveSequence("t", b"ACGTTCGT"), s.AllwaveSequence("long", b"ACGTACGTACGT")]
+    # forward, one mismatch: 7 matches over 8 aligned columns
     r = s.AlignmentResult(0, 1, 0, 8, 0, 8, False, b"MMMMXMMM", -5, 7, 8)
-    f = s.alignment_to_paf(r, seqs).split("\t")
-    assert f[:9] == ["q", "8", "0", "8", "+", "t", "8", "0", "8"] and f[9:12] == ["7", "8", "60"]
-    assert f[12] == "cg:Z:4=1X3="
+    assert s.alignment_to_paf(r, seqs) == "q\t8\t0\t8\t+\tt\t8\t0\t8\t7\t8\t60\tgi:f:0.875000\tcg:Z:4=1X3="
+    # reverse strand with gaps (test_wfa2_cigar_debug's MMMMMMMMIIII: WFA 'I' consumes the target and is
+    # written as 'D'): block_len = max(8, 12) = 12 although only 8 columns are M/X
+    r = s.AlignmentResult(0, 2, 0, 8, 0, 12, True, b"MMMMMMMMIIII", -16, 8, 8)
+    assert s.alignment_to_paf(r, seqs) == "q\t8\t0\t8\t-\tlong\t12\t0\t12\t8\t12\t60\tgi:f:1.000000\tcg:Z:8=4D"
+    # block_len follows the longer side, here the query (WFA 'D' consumes the query -> 'I')
+    r = s.AlignmentResult(2, 0, 0, 12, 0, 8, False, b"MMMMDDDDMMMM", -16, 8, 8)
+    assert s.alignment_to_paf(r, seqs) == "long\t12\t0\t12\t+\tq\t8\t0\t8\t8\t12\t60\tgi:f:1.000000\tcg:Z:4=4I4="
+    # failed alignment (allwave/src/alignment.rs:40-55): empty CIGAR, alignment_length 0 -> identity 0.0
+    r = s.AlignmentResult(0, 1, 0, 0, 0, 0, False, b"", 2**31 - 1, 0, 0)
+    assert s.alignment_to_paf(r, seqs) == "q\t8\t0\t0\t+\tt\t8\t0\t0\t0\t0\t60\tgi:f:0.000000\tcg:Z:"
+    # identity is rounded to six decimals like Rust's {:.6}
+    r = s.AlignmentResult(0, 1, 0, 8, 0, 8, False, b"MMXMMXMM", -10, 2, 3)
+    assert "\tgi:f:0.666667\t" in s.alignment_to_paf(r, seqs)
+    # what the writer emits is what the --paf reader takes back (src/seqrush.rs:529-560 looks for cg:Z: in any tag)
     from seqrush_b200.seqrush import parse_paf_line
-    r.is_reverse = True  # what the writer emits is what the --paf reader takes back (src/seqrush.rs:529-560)
+    r = s.AlignmentResult(0, 1, 0, 8, 0, 8, True, b"MMMMXMMM", -5, 7, 8)
     assert parse_paf_line(s.alignment_to_paf(r, seqs) + "\n") == ("q", 0, 8, "-", "t", 0, 8, "4=1X3=")
 
 
