@@ -3,13 +3,15 @@ import sys, time, json
 sys.path.insert(0, ".")
 import numpy as np, torch
 import seqrush_b200 as s
-from bench import make_workload, all_pairs
+from bench import WORKLOADS
+from seqrush_b200 import synth
 
 wl = sys.argv[1] if len(sys.argv) > 1 else "c2"
 npairs = int(sys.argv[2]) if len(sys.argv) > 2 else 5000
 configs = [tuple(int(x) for x in c.split("x")) for c in (sys.argv[3].split(",") if len(sys.argv) > 3 else ["256x2"])]
-ids, seqs, desc = make_workload(wl)
-pairs = all_pairs(len(seqs))
+cfg_name, n_seq, L = WORKLOADS[wl][:3]
+ids, seqs = synth.make_config(cfg_name, n=n_seq, length=L)
+pairs = synth.all_pairs(len(seqs))
 rng = np.random.default_rng(0)
 pairs = pairs[np.sort(rng.choice(pairs.shape[0], size=min(npairs, pairs.shape[0]), replace=False))]
 ctx = s.Context(0)

@@ -84,7 +84,7 @@ struct srgpu_ctx {
   int lbits = 3;              // log2(bits per packed symbol): 1, 2 or 3
   uint32_t max_pk_words = 0;  // packed words of the longest sequence incl. guards
   int smem_budget = 96 * 1024;  // dynamic shared memory a kernel may use for staged sequences
-  bool stage_seqs = false;      // align_kernel: also stage the two sequences (SRGPU_STAGE_SEQS=1)
+  int stage_seqs = -1;          // align_kernel: stage the two sequences (-1: when the CTAs per SM are kept; SRGPU_STAGE_SEQS=0/1)
   DevBuf<uint32_t> d_len;
   std::vector<uint32_t> h_len;
   std::vector<uint64_t> h_pos_off;
@@ -156,7 +156,7 @@ extern "C" int srgpu_ctx_create(int device, void* stream, srgpu_ctx** out) {
   }
   for (int i = 0; i < 6; ++i) CK(cudaEventCreate(&c->ev[i]));
   if (const char* e = getenv("SRGPU_SMEM_BUDGET")) c->smem_budget = atoi(e);  // tuning: 0 = never stage sequences
-  if (const char* e = getenv("SRGPU_STAGE_SEQS")) c->stage_seqs = atoi(e) != 0;
+  if (const char* e = getenv("SRGPU_STAGE_SEQS")) c->stage_seqs = atoi(e) != 0 ? 1 : 0;
   *out = c;
   return SRGPU_OK;
 }
@@ -428,18 +428,12 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
   }
   const uint32_t maxlen = c->max_len;
   // orient_kernel stages its three packed sequences (query forward, query RC, target) in dynamic shared
-  // memory when they fit. align_kernel reads its two sequences from global memory through L1 (measured
-  // on the 1500-pair c2 slice: 873 ms against 845 ms staged, profiles/r02a_*) and spends its shared
-  // memory on the double-buffered row staging of the score step instead; SRGPU_STAGE_SEQS=1 stages them
-  // as well when both fit the budget.
-  size_t smem_seqs = (size_t)2 * c->max_pk_words * 4;
+  // memory when they fit; align_kernel its two, next to the per-warp row staging buffers of the score
+  // step, when the launch shape keeps its CTAs per SM with them (else they are read from global memory
+  // through L1: the first packed window of every cell then waits for L1/L2, 12 % of all warp stall
+  // samples in profiles/r02d_*). SRGPU_STAGE_SEQS=0 / 1 forces either way.
   size_t smem_orient = (size_t)3 * c->max_pk_words * 4;
-  uint32_t smem_seq_words = c->max_pk_words;
   if (smem_orient > (size_t)c->smem_budget) smem_orient = 0;
-  if (!c->stage_seqs || smem_seqs > (size_t)c->smem_budget) {
-    smem_seqs = 0;
-    smem_seq_words = 0;
-  }
   // launch shape: 128 threads x 4 CTAs/SM up to ~70 kb; longer sequences have wavefronts wide enough to
   // keep 8 warps busy per pair and their staged sequences leave room for 2-3 CTAs only (measured on the
   // 100 kb slice: 256x2 36.9 Mbp/s, 128x4 29.1)
@@ -448,7 +442,19 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
     threads = 256;
     ctas_per_sm = 2;
   }
-  const size_t smem = smem_seqs + (size_t)(threads / 32) * 2 * STAGE_INTS * sizeof(int32_t);
+  const size_t smem_rows = (size_t)(threads / 32) * STAGE_INTS * sizeof(int32_t);
+  size_t smem_seqs = (size_t)2 * c->max_pk_words * 4;
+  uint32_t smem_seq_words = c->max_pk_words;
+  {
+    const size_t per_sm = 227 * 1024, static_smem = 13 * 1024 + 1024;  // CtaShared + the per-CTA reservation
+    const bool fits = (static_smem + smem_rows + smem_seqs) * (size_t)ctas_per_sm <= per_sm;
+    const bool want = c->stage_seqs < 0 ? fits : c->stage_seqs != 0;
+    if (!want || smem_seqs > (size_t)c->smem_budget || static_smem + smem_rows + smem_seqs > per_sm) {
+      smem_seqs = 0;
+      smem_seq_words = 0;
+    }
+  }
+  const size_t smem = smem_seqs + smem_rows;
   const int resident = std::min(ctas_per_sm, align_occupancy(threads, ctas_per_sm, smem));
   int grid = c->n_sm * resident;
   if ((uint64_t)grid > n_pairs) grid = (int)n_pairs;

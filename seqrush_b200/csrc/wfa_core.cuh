@@ -180,7 +180,7 @@ struct Ctx {
   CtaShared* sh;
   int tid, nt;
   int parity;
-  int32_t* stage;  // device: shared-memory staging of the source-row slices of a chunk (per warp 2 x STAGE_INTS)
+  int32_t* stage;  // device: shared-memory staging of the source-row slices of a chunk (STAGE_INTS per warp)
 };
 
 // Staged source rows of one chunk: seven rows (o1, o2, i1, i2, d1, d2, mis in the order of DS_O1..DS_MIS),
@@ -1079,18 +1079,24 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
   // Chunks of both directions are claimed from one shared counter; inside a direction the two
   // fringe chunks (masked reads, per-cell trims: ~1.5x an interior chunk) go first.
   // The seven source-row slices of a chunk are staged in shared memory by asynchronous 16-byte
-  // copies, double-buffered per warp: a warp claims its NEXT chunk and starts that chunk's copies
-  // before it computes the current one, so the global-memory latency of the row reads (38 % of all
-  // warp stall samples when the rows were read straight into registers: profiles/r02b_*) is covered
-  // by one chunk of compute instead of being waited for. The copies cost no registers.
+  // copies (one buffer per warp): a warp moves the staged slices of its current chunk into
+  // registers, then claims its NEXT chunk and starts that chunk's copies before it computes the
+  // current one, so the global-memory latency of the row reads (38 % of all warp stall samples when
+  // the rows were read straight into registers: profiles/r02b_*) is covered by one chunk of compute
+  // instead of being waited for. The copies in flight cost no registers.
   int n_dir = -1, n_kb = 0;
-  auto claim_next = [&]() {
+  auto claim_issue = [&]() -> int {  // lane 0 takes the next chunk index; the value is consumed by claim_decode
     int claim = 0;
 #if WFA_DEVICE
     if (lane == 0) claim = atomicAdd(&cx.sh->chunk_ctr, 1);
-    claim = __shfl_sync(0xffffffffu, claim, 0);
 #else
     claim = cx.sh->chunk_ctr++;
+#endif
+    return claim;
+  };
+  auto claim_decode = [&](int claim) {
+#if WFA_DEVICE
+    claim = __shfl_sync(0xffffffffu, claim, 0);
 #endif
     if (claim >= nch_all) {
       n_dir = -1;
@@ -1104,33 +1110,31 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
     n_kb = sn[DS_LOAL] + ci * CH;
   };
 #if WFA_DEVICE
-  int32_t* const wstage = cx.stage + warp * (2 * STAGE_INTS);
-  int stage = 0;
-  // copies of the slices [kb-4, kb+132) of the seven source rows of chunk (pdir, pkb) into buffer pst.
+  int32_t* const wstage = cx.stage + warp * STAGE_INTS;
+  // copies of the slices [kb-4, kb+132) of the seven source rows of chunk (pdir, pkb) into the warp's buffer.
   // Segments that start beyond hi+4 are not read (they would leave the row allocation, which keeps
   // 8 diagonals of slack); whatever an unread segment holds is outside every source wavefront and is
   // masked (fringe chunk) or belongs to lanes that neither compute a valid cell nor store.
-  auto prefetch = [&](int pdir, int pkb, int pst) {
+  auto prefetch = [&](int pdir, int pkb) {
     if (pdir >= 0) {
       const volatile int* sp = cx.sh->ds[pdir];
       const int phi = sp[DS_HI] + 4;
-      int32_t* sb = wstage + pst * STAGE_INTS;
       const int ks = pkb - 4 + 4 * lane;   // segment `lane`
       const int ks2 = ks + 128;            // segments 32, 33 (lanes 0 and 1)
       const bool ok0 = ks <= phi, ok1 = lane < 2 && ks2 <= phi;
 #pragma unroll
       for (int r = 0; r < 7; ++r) {
         const int off = sp[DS_O1 + r];
-        if (ok0) cp_async16(sb + r * STAGE_ROW + 4 * lane, ring + (off + ks));
-        if (ok1) cp_async16(sb + r * STAGE_ROW + 128 + 4 * lane, ring + (off + ks2));
+        if (ok0) cp_async16(wstage + r * STAGE_ROW + 4 * lane, ring + (off + ks));
+        if (ok1) cp_async16(wstage + r * STAGE_ROW + 128 + 4 * lane, ring + (off + ks2));
       }
     }
     cp_async_commit();
   };
 #endif
-  claim_next();
+  claim_decode(claim_issue());
 #if WFA_DEVICE
-  prefetch(n_dir, n_kb, 0);
+  prefetch(n_dir, n_kb);
 #endif
   while (true) {
     const int dir = n_dir, kb = n_kb;
@@ -1147,36 +1151,33 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
       acc_dir = dir;
     }
     if (done) break;  // a warp that claimed nothing has acc_dir == dir == -1
+    const int k0 = kb + 4 * lane;
 #if WFA_DEVICE
-    __syncwarp();  // every lane has finished reading the other buffer (previous chunk)
-#endif
-    claim_next();
-#if WFA_DEVICE
-    prefetch(n_dir, n_kb, stage ^ 1);
-    cp_async_wait<1>();  // this chunk's copies have landed (the group just committed may still fly)
+    const int next_claim = claim_issue();  // the shared-memory atomic's latency hides behind the reads below
+    cp_async_wait<0>();                    // this chunk's copies have landed
     __syncwarp();
+    // own four cells of every row with one 128-bit shared-memory read, the k0-1 / k0+4 neighbours
+    // with scalar reads of the same staged slice
+    const int32_t* sb = wstage + 4 + 4 * lane;
+    I4 vo1 = ld4(sb), vo2 = ld4(sb + STAGE_ROW), vi1 = ld4(sb + 2 * STAGE_ROW), vi2 = ld4(sb + 3 * STAGE_ROW);
+    I4 vd1 = ld4(sb + 4 * STAGE_ROW), vd2 = ld4(sb + 5 * STAGE_ROW), vmis = ld4(sb + 6 * STAGE_ROW);
+    int32_t o1L = sb[-1], o2L = sb[STAGE_ROW - 1], i1L = sb[2 * STAGE_ROW - 1], i2L = sb[3 * STAGE_ROW - 1];
+    int32_t o1R = sb[4], o2R = sb[STAGE_ROW + 4], d1R = sb[4 * STAGE_ROW + 4], d2R = sb[5 * STAGE_ROW + 4];
+    __syncwarp();  // every lane holds its slices in registers: the buffer is free for the next chunk
+    claim_decode(next_claim);
+    prefetch(n_dir, n_kb);
 #endif
     const volatile int* su = cx.sh->ds[dir];
     const int lo = su[DS_LO], hi = su[DS_HI];
     const int fl = su[DS_FLAGS];
     const bool a_i1 = fl & 1, a_i2 = fl & 2, a_d1 = fl & 4, a_d2 = fl & 8;
     const int dp0 = su[DS_P0], dt0 = su[DS_T0], drev = su[DS_REV], dcend = su[DS_CEND];
-    const int k0 = kb + 4 * lane;
     int32_t ins1[4], ins2[4], del1[4], del2[4], mx[4];
     bool vm[4];
     PROF_T(tc0);
     // lanes of the last chunk that lie wholly beyond hi do not store (they would leave the row)
     const bool lane_act = k0 <= hi;
-#if WFA_DEVICE
-    // own four cells of every row with one 128-bit shared-memory read, the k0-1 / k0+4 neighbours
-    // with scalar reads of the same staged slice
-    const int32_t* sb = wstage + stage * STAGE_INTS + 4 + 4 * lane;
-    stage ^= 1;
-    I4 vo1 = ld4(sb), vo2 = ld4(sb + STAGE_ROW), vi1 = ld4(sb + 2 * STAGE_ROW), vi2 = ld4(sb + 3 * STAGE_ROW);
-    I4 vd1 = ld4(sb + 4 * STAGE_ROW), vd2 = ld4(sb + 5 * STAGE_ROW), vmis = ld4(sb + 6 * STAGE_ROW);
-    int32_t o1L = sb[-1], o2L = sb[STAGE_ROW - 1], i1L = sb[2 * STAGE_ROW - 1], i2L = sb[3 * STAGE_ROW - 1];
-    int32_t o1R = sb[4], o2R = sb[STAGE_ROW + 4], d1R = sb[4 * STAGE_ROW + 4], d2R = sb[5 * STAGE_ROW + 4];
-#else
+#if !WFA_DEVICE
     const int lo_al = su[DS_LOAL];
     const int kq = lane_act ? k0 : lo_al;
     const int32_t* const r_o1 = ring + (su[DS_O1] + kq);
@@ -1190,6 +1191,7 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
     // host emulation: one "lane", so the k0-1 / k0+4 neighbours are plain reads
     int32_t o1L = r_o1[-1], o2L = r_o2[-1], i1L = r_i1[-1], i2L = r_i2[-1];
     int32_t o1R = r_o1[4], o2R = r_o2[4], d1R = r_d1[4], d2R = r_d2[4];
+    claim_decode(claim_issue());
 #endif
     const bool interior = kb >= su[DS_INLO] && kb + CH - 1 <= su[DS_INHI];  // warp-uniform
     if (!interior) {
