@@ -207,6 +207,48 @@ int srgpu_uf_merge_roots(srgpu_uf* uf, const void* d_peer_roots, uint64_t n);
 int srgpu_uf_compress_async(srgpu_uf* uf);
 int srgpu_uf_merge_gathered(srgpu_uf* uf, const void* d_gathered, uint64_t n, int world, int my_rank);
 
+/* ---- Graph build from the partition (the consumer of the union-find): the reference's
+ * write_bidirected_gfa (src/bidirected_gfa_writer.rs:8-167) with --skip-sgd --skip-groom --skip-topo =
+ * build_bidirected_graph_with_options (src/bidirected_builder.rs:17-289) -> compact + renumber unless
+ * --no-compact (src/bidirected_ops.rs:75-478) -> validate_paths_match_sequences (src/seqrush.rs:1741-1798) ->
+ * write_gfa (src/bidirected_ops.rs:880-925).
+ *
+ * srgpu_graph_build runs on the device: bulk canonical roots (two finds per base, :48-49), first-seen node
+ * numbering by a prefix sum, node bases, oriented path steps, and the complement-aware edge set in the form of
+ * each edge's first occurrence (add_edge, src/bidirected_ops.rs:813-825). The union-find must hold the
+ * invariant of SeqRush::new (every forward Pos united with its reverse, src/seqrush.rs:324-328).
+ *
+ * Node base. The reference reads it at the offset of the union-find ROOT (:176-182), which for uf_rush depends
+ * on union order and thread interleaving; for a component that mixes forward and reverse-complement members
+ * that choice fixes the node's orientation. `representatives` == NULL uses this library's canonical
+ * representative (the first-seen member, so the first step through a node is always '+'); otherwise
+ * representatives[i] (i < total_length) is a Pos inside the component of position i whose offset supplies the
+ * base -- pass the roots of a sequential uf_rush run to reproduce the reference at -t 1 byte for byte.
+ *
+ * L lines are written sorted by (from, to) handle; the reference writes them in HashSet iteration order, which
+ * differs from process to process. */
+typedef struct srgpu_graph srgpu_graph;
+int srgpu_graph_build(srgpu_ctx* ctx, srgpu_uf* uf, const uint64_t* representatives, srgpu_graph** out);
+/* The same object from caller-supplied parts (host only, no device): single-base nodes 1..n_nodes, per-path
+ * handle lists (concatenated), stored edges as (from, to) handle pairs, and the sequences the paths must spell. */
+int srgpu_graph_from_parts(uint64_t n_nodes, const uint8_t* node_bases, uint32_t n_paths, const uint64_t* path_lens,
+                           const uint64_t* steps, uint64_t n_edges, const uint64_t* from_to, const srgpu_seqview* seqs,
+                           srgpu_graph** out);
+int srgpu_graph_compact(srgpu_graph* g); /* BidirectedGraph::compact + renumber_nodes_sequentially */
+uint64_t srgpu_graph_node_count(srgpu_graph* g);
+uint64_t srgpu_graph_edge_count(srgpu_graph* g);
+uint64_t srgpu_graph_path_count(srgpu_graph* g);
+uint64_t srgpu_graph_path_length(srgpu_graph* g, uint32_t path);
+/* handles = (node_id << 1) | is_reverse (src/bidirected_graph.rs:6-48) */
+int srgpu_graph_path_steps(srgpu_graph* g, uint32_t path, uint64_t* out, uint64_t cap);
+int64_t srgpu_graph_node_sequence(srgpu_graph* g, uint64_t node_id, char* buf, uint64_t cap); /* length, -1 if absent */
+int srgpu_graph_edges(srgpu_graph* g, uint64_t* from_to, uint64_t cap_edges); /* sorted (from, to) handle pairs */
+/* validate + write; names[i] = id of sequence i (P line names). *text is released with srgpu_free. */
+int srgpu_graph_gfa_text(srgpu_graph* g, const char* const* names, uint32_t n_names, char** text, uint64_t* len);
+int srgpu_graph_write_gfa(srgpu_graph* g, const char* const* names, uint32_t n_names, const char* path);
+int srgpu_graph_stats(srgpu_graph* g, uint64_t* uncompacted_nodes, uint32_t* rounds, uint32_t* merged_chains);
+void srgpu_graph_free(srgpu_graph* g);
+
 #ifdef __cplusplus
 }
 #endif

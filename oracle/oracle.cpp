@@ -381,6 +381,440 @@ extern "C" int orc_process_alignment(void* u, const char* cigar, const uint8_t* 
 }
 
 // ---------------------------------------------------------------------------
+// Graph build from the union-find, compaction and GFA text -- literal restatement of
+//   SeqRush::build_bidirected_graph_with_options (src/bidirected_builder.rs:17-289, apply_sort=false),
+//   BidirectedGraph::{add_node, add_edge, build_path, verify_path_edges, compact, find_simple_components,
+//   merge_component_v2, renumber_nodes_sequentially, apply_node_id_mapping, write_gfa}
+//   (src/bidirected_ops.rs:22-89, 91-478, 804-825, 871-925, 1049-1068), Handle / BiEdge / reverse_complement
+//   (src/bidirected_graph.rs), and the driver write_bidirected_gfa (src/bidirected_gfa_writer.rs:8-167) with
+//   --skip-sgd --skip-groom --skip-topo (the Ygs phases are then no-ops).
+// Quadratic where the reference is quadratic (key scan :96-119, are_perfect_neighbors scanning every path per
+// candidate, merge_component_v2 scanning every path and edge per chain): small inputs and configs[0] only.
+// HashMap/HashSet iteration order is unspecified in Rust; it is observable in exactly two places: the key scan of
+// the builder (first match wins -- on the production path nothing ever matches, distinct roots are distinct
+// components) and the order of the L lines in write_gfa, which are therefore emitted SORTED here and compared
+// sorted everywhere (SURVEY.md 8(c) rule 4).
+// ---------------------------------------------------------------------------
+#include <algorithm>
+#include <map>
+#include <set>
+#include <unordered_map>
+#include <unordered_set>
+namespace ograph {
+typedef uint64_t Handle;  // (node_id << 1) | is_reverse, src/bidirected_graph.rs:6-48
+static inline Handle mk(uint64_t id, bool rev) { return (id << 1) | (rev ? 1u : 0u); }
+static inline uint64_t nid(Handle h) { return h >> 1; }
+static inline bool isrev(Handle h) { return (h & 1) != 0; }
+static inline Handle flip(Handle h) { return h ^ 1; }
+typedef std::pair<Handle, Handle> Edge;
+static std::vector<uint8_t> revcomp(const std::vector<uint8_t>& s) {  // src/bidirected_graph.rs:58-71
+  std::vector<uint8_t> o(s.rbegin(), s.rend());
+  for (auto& b : o) {
+    switch (b) {
+      case 'A': case 'a': b = 'T'; break;
+      case 'T': case 't': b = 'A'; break;
+      case 'C': case 'c': b = 'G'; break;
+      case 'G': case 'g': b = 'C'; break;
+      case 'N': case 'n': b = 'N'; break;
+      default: break;
+    }
+  }
+  return o;
+}
+struct Graph {
+  std::vector<std::vector<uint8_t>> seq;  // index = node id
+  std::vector<char> present;
+  std::set<Edge> edges;  // a set; iteration order is never relied on
+  std::vector<std::pair<std::string, std::vector<Handle>>> paths;
+  void add_node(uint64_t id, std::vector<uint8_t> s) {  // :804-810
+    if (id >= seq.size()) {
+      seq.resize(id + 1);
+      present.resize(id + 1, 0);
+    }
+    seq[id] = std::move(s);
+    present[id] = 1;
+  }
+  void add_edge(Handle from, Handle to) {  // :813-825
+    const Edge e(from, to), c(flip(to), flip(from));
+    if (!edges.count(e) && !edges.count(c)) edges.insert(e);
+  }
+  void verify_path_edges() {  // :1049-1068
+    for (auto& p : paths)
+      for (size_t i = 0; i + 1 < p.second.size(); ++i) {
+        const Edge e(p.second[i], p.second[i + 1]), c(flip(p.second[i + 1]), flip(p.second[i]));
+        if (!edges.count(e) && !edges.count(c)) edges.insert(e);
+      }
+  }
+  // :113-275
+  std::vector<std::vector<Handle>> find_simple_components() const {
+    std::vector<std::vector<Handle>> components;
+    std::unordered_set<Handle> visited;
+    std::unordered_set<uint64_t> merged_nodes;
+    std::unordered_map<Handle, std::vector<Handle>> fwd, bwd;
+    for (const Edge& e : edges) {
+      fwd[e.first].push_back(e.second);
+      bwd[e.second].push_back(e.first);
+      fwd[flip(e.second)].push_back(flip(e.first));
+      bwd[flip(e.first)].push_back(flip(e.second));
+    }
+    auto deg = [](const std::unordered_map<Handle, std::vector<Handle>>& m, Handle h) -> size_t {
+      auto it = m.find(h);
+      return it == m.end() ? 0 : it->second.size();
+    };
+    auto perfect = [&](Handle from, Handle to) -> bool {  // :141-190
+      for (auto& p : paths) {
+        const std::vector<Handle>& st = p.second;
+        size_t visits = 0, trans = 0;
+        for (size_t i = 0; i < st.size(); ++i)
+          if (st[i] == from) {
+            ++visits;
+            if (i + 1 < st.size()) {
+              if (st[i + 1] == to) ++trans;
+              else return false;
+            } else {
+              return false;
+            }
+          }
+        if (visits > 0 && visits != trans) return false;
+        const Handle fr = flip(from), tr = flip(to);
+        size_t v2 = 0, t2 = 0;
+        for (size_t i = 0; i < st.size(); ++i)
+          if (st[i] == tr) {
+            ++v2;
+            if (i + 1 < st.size()) {
+              if (st[i + 1] == fr) ++t2;
+              else return false;
+            } else {
+              return false;
+            }
+          }
+        if (v2 > 0 && v2 != t2) return false;
+      }
+      return true;
+    };
+    for (uint64_t id = 0; id < seq.size(); ++id) {
+      if (!present[id]) continue;
+      for (int o = 0; o < 2; ++o) {
+        const Handle handle = mk(id, o == 1);
+        if (visited.count(handle)) continue;
+        if (deg(fwd, handle) == 1) {
+          std::vector<Handle> chain{handle};
+          visited.insert(handle);
+          Handle cur = handle;
+          while (true) {
+            auto it = fwd.find(cur);
+            if (it == fwd.end()) break;
+            if (it->second.size() != 1) break;
+            const Handle next = it->second[0];
+            if (deg(bwd, next) != 1 || visited.count(next)) break;
+            if (!perfect(cur, next)) break;
+            chain.push_back(next);
+            visited.insert(next);
+            cur = next;
+            if (deg(fwd, next) != 1) break;
+          }
+          if (chain.size() >= 2) {
+            bool already = false;
+            for (Handle h : chain)
+              if (merged_nodes.count(nid(h))) {
+                already = true;
+                break;
+              }
+            if (!already) {
+              for (Handle h : chain) merged_nodes.insert(nid(h));
+              components.push_back(chain);
+            }
+          }
+        }
+      }
+    }
+    return components;
+  }
+  // :277-478
+  bool merge_component_v2(const std::vector<Handle>& handles) {
+    if (handles.size() < 2) return false;
+    const size_t n = handles.size();
+    std::unordered_map<Handle, size_t> mapping;  // handle -> chain position (the other tuple fields are unused)
+    std::vector<uint8_t> new_seq;
+    for (Handle h : handles) {
+      if (nid(h) < seq.size() && present[nid(h)]) {
+        if (isrev(h)) {
+          auto r = revcomp(seq[nid(h)]);
+          new_seq.insert(new_seq.end(), r.begin(), r.end());
+        } else {
+          new_seq.insert(new_seq.end(), seq[nid(h)].begin(), seq[nid(h)].end());
+        }
+      }
+    }
+    const uint64_t new_id = seq.size();  // next_node_id(), :692-694
+    const Handle nf = mk(new_id, false), nr = mk(new_id, true);
+    for (size_t i = 0; i < n; ++i) {
+      mapping[handles[i]] = i;
+      mapping[flip(handles[i])] = n - 1 - i;
+    }
+    std::vector<Handle> rev_chain(n);
+    for (size_t i = 0; i < n; ++i) rev_chain[i] = flip(handles[n - 1 - i]);
+    for (auto& p : paths) {
+      const std::vector<Handle>& st = p.second;
+      size_t i = 0;
+      while (i < st.size()) {
+        auto it = mapping.find(st[i]);
+        if (it != mapping.end()) {
+          if (it->second == 0) {
+            if (i + n <= st.size()) {
+              bool complete = true;
+              for (size_t j = 0; j < n; ++j)
+                if (st[i + j] != handles[j]) {
+                  complete = false;
+                  break;
+                }
+              if (complete) {
+                i += n;
+                continue;
+              }
+            }
+          }
+          if (st[i] == rev_chain[0]) {
+            if (i + n <= st.size()) {
+              bool complete = true;
+              for (size_t j = 0; j < n; ++j)
+                if (st[i + j] != rev_chain[j]) {
+                  complete = false;
+                  break;
+                }
+              if (complete) {
+                i += n;
+                continue;
+              }
+            }
+          }
+          return false;
+        }
+        ++i;
+      }
+    }
+    add_node(new_id, new_seq);
+    for (auto& p : paths) {
+      std::vector<Handle>& st = p.second;
+      std::vector<Handle> ns;
+      size_t i = 0;
+      while (i < st.size()) {
+        if (i + n <= st.size()) {
+          bool f = true;
+          for (size_t j = 0; j < n; ++j)
+            if (st[i + j] != handles[j]) {
+              f = false;
+              break;
+            }
+          if (f) {
+            ns.push_back(nf);
+            i += n;
+            continue;
+          }
+          bool r = true;
+          for (size_t j = 0; j < n; ++j)
+            if (st[i + j] != rev_chain[j]) {
+              r = false;
+              break;
+            }
+          if (r) {
+            ns.push_back(nr);
+            i += n;
+            continue;
+          }
+        }
+        ns.push_back(st[i]);
+        ++i;
+      }
+      st.swap(ns);
+    }
+    const Handle first = handles[0], last = handles[n - 1];
+    std::unordered_set<uint64_t> merged_ids;
+    for (Handle h : handles) merged_ids.insert(nid(h));
+    std::set<Edge> ne;
+    for (const Edge& e : edges) {
+      const bool fi = merged_ids.count(nid(e.first)) != 0, ti = merged_ids.count(nid(e.second)) != 0;
+      if (fi && ti) continue;
+      if (!fi && !ti) {
+        ne.insert(e);
+      } else if (fi && !ti) {
+        if (e.first == last) ne.insert(Edge(nf, e.second));
+        if (e.first == flip(first)) ne.insert(Edge(nr, e.second));
+      } else {
+        if (e.second == first) ne.insert(Edge(e.first, nf));
+        if (e.second == flip(last)) ne.insert(Edge(e.first, nr));
+      }
+    }
+    edges.swap(ne);
+    for (Handle h : handles)
+      if (nid(h) < seq.size()) present[nid(h)] = 0;
+    return true;
+  }
+  void compact() {  // :91-112
+    bool compacted = true;
+    while (compacted) {
+      compacted = false;
+      for (auto& comp : find_simple_components())
+        if (comp.size() >= 2 && merge_component_v2(comp)) compacted = true;
+    }
+  }
+  void renumber() {  // :75-89 + :22-73
+    std::vector<uint64_t> map(seq.size(), 0);
+    uint64_t next = 1;
+    for (uint64_t id = 0; id < seq.size(); ++id)
+      if (present[id]) map[id] = next++;
+    std::vector<std::vector<uint8_t>> ns(next);
+    std::vector<char> np(next, 0);
+    for (uint64_t id = 0; id < seq.size(); ++id)
+      if (present[id]) {
+        ns[map[id]] = seq[id];
+        np[map[id]] = 1;
+      }
+    if (next == 1) {  // max_new_id = 0 -> vec![None; 1]
+      ns.assign(1, {});
+      np.assign(1, 0);
+    }
+    seq.swap(ns);
+    present.swap(np);
+    auto mh = [&](Handle h) -> Handle { return mk(nid(h) < map.size() && map[nid(h)] ? map[nid(h)] : nid(h), isrev(h)); };
+    std::set<Edge> ne;
+    for (const Edge& e : edges) ne.insert(Edge(mh(e.first), mh(e.second)));
+    edges.swap(ne);
+    for (auto& p : paths)
+      for (auto& h : p.second) h = mh(h);
+  }
+  std::string gfa() const {  // :880-925, L lines sorted
+    std::string o = "H\tVN:Z:1.0\n";
+    for (uint64_t id = 0; id < seq.size(); ++id)
+      if (present[id]) {
+        o += "S\t" + std::to_string(id) + "\t";
+        o.append((const char*)seq[id].data(), seq[id].size());
+        o += "\n";
+      }
+    for (const Edge& e : edges)
+      o += "L\t" + std::to_string(nid(e.first)) + "\t" + (isrev(e.first) ? "-" : "+") + "\t" + std::to_string(nid(e.second)) +
+           "\t" + (isrev(e.second) ? "-" : "+") + "\t0M\n";
+    for (auto& p : paths) {
+      o += "P\t" + p.first + "\t";
+      for (size_t i = 0; i < p.second.size(); ++i) {
+        if (i) o += ",";
+        o += std::to_string(nid(p.second[i]));
+        o += isrev(p.second[i]) ? "-" : "+";
+      }
+      o += "\t*\n";
+    }
+    return o;
+  }
+};
+}  // namespace ograph
+
+// build (+ compact + renumber unless no_compact) + validate_paths_match_sequences + write_gfa.
+// ids: n_seqs NUL-terminated names. rep_out (optional, total_len entries): the union-find representative
+// (uf.find of the forward Pos) of every position at build time -- what decides the node base (:176-182).
+// Returns a malloc'd NUL-terminated GFA text (free with orc_free), nullptr when path validation fails.
+extern "C" char* orc_build_gfa(void* u, const uint8_t* const* seq_data, const uint64_t* seq_len, uint32_t n_seqs,
+                               const char* const* ids, int no_compact, uint64_t* rep_out, uint64_t* n_nodes_uncompacted) {
+  BUF* uf = (BUF*)u;
+  ograph::Graph g;
+  std::vector<uint64_t> off(n_seqs);
+  uint64_t acc = 0;
+  for (uint32_t i = 0; i < n_seqs; ++i) {
+    off[i] = acc;
+    acc += seq_len[i];
+  }
+  auto same = [&](uint64_t a, uint64_t b) { return a == b || uf->uf.find(a) == uf->uf.find(b); };
+  std::unordered_map<uint64_t, uint64_t> union_to_node;
+  uint64_t next_node_id = 1;
+  for (uint32_t si = 0; si < n_seqs; ++si) {
+    std::vector<ograph::Handle> steps;
+    for (uint64_t i = 0; i < seq_len[si]; ++i) {
+      const uint64_t gp = off[si] + i;
+      const uint64_t pos_fwd = gp << 1, pos_rev = (gp << 1) | 1;
+      const uint64_t union_fwd = uf->uf.find(pos_fwd), union_rev = uf->uf.find(pos_rev);
+      if (rep_out) rep_out[gp] = union_fwd;
+      uint64_t union_rep;
+      if (union_to_node.count(union_fwd)) {
+        union_rep = union_fwd;
+      } else if (union_to_node.count(union_rev)) {
+        union_rep = union_rev;
+      } else {
+        const uint64_t fwd_root = uf->uf.find(pos_fwd), rev_root = uf->uf.find(pos_rev);
+        if (union_to_node.count(fwd_root)) {
+          union_rep = fwd_root;
+        } else if (union_to_node.count(rev_root)) {
+          union_rep = rev_root;
+        } else {
+          bool found = false;
+          uint64_t existing = 0;
+          for (auto& kv : union_to_node) {  // :96-119
+            if (same(union_fwd, kv.first) || same(union_rev, kv.first)) {
+              found = true;
+              existing = kv.first;
+              break;
+            }
+          }
+          union_rep = found ? existing : union_fwd;
+        }
+      }
+      uint64_t node_id;
+      uint8_t node_base;
+      auto it = union_to_node.find(union_rep);
+      if (it != union_to_node.end()) {
+        node_id = it->second;
+        node_base = (node_id < g.seq.size() && g.present[node_id]) ? g.seq[node_id][0] : seq_data[si][i];
+      } else {
+        node_id = next_node_id++;
+        union_to_node[union_rep] = node_id;
+        if (same(pos_fwd, union_rep) && !union_to_node.count(union_fwd)) union_to_node[union_fwd] = node_id;
+        if (same(pos_rev, union_rep) && !union_to_node.count(union_rev)) union_to_node[union_rev] = node_id;
+        uint8_t base = seq_data[si][i];
+        const uint64_t ro = union_rep >> 1;
+        for (uint32_t k = 0; k < n_seqs; ++k)  // find_sequence_for_position, :327-333
+          if (ro >= off[k] && ro < off[k] + seq_len[k]) {
+            base = seq_data[k][ro - off[k]];
+            break;
+          }
+        g.add_node(node_id, std::vector<uint8_t>{base});
+        node_base = base;
+      }
+      auto up = [](uint8_t c) -> uint8_t { return (c >= 'a' && c <= 'z') ? (uint8_t)(c - 32) : c; };
+      const uint8_t e = up(seq_data[si][i]), nb = up(node_base);
+      const bool need_reverse = (nb == 'A' && e == 'T') || (nb == 'T' && e == 'A') || (nb == 'C' && e == 'G') || (nb == 'G' && e == 'C');
+      steps.push_back(ograph::mk(node_id, need_reverse));
+    }
+    g.paths.emplace_back(std::string(ids[si]), std::move(steps));
+  }
+  for (auto& p : g.paths)
+    for (size_t i = 0; i + 1 < p.second.size(); ++i) g.add_edge(p.second[i], p.second[i + 1]);
+  g.verify_path_edges();
+  g.verify_path_edges();
+  if (n_nodes_uncompacted) *n_nodes_uncompacted = next_node_id - 1;
+  if (!no_compact) {
+    g.compact();
+    g.renumber();
+  }
+  // validate_paths_match_sequences (src/seqrush.rs:1741-1798)
+  for (uint32_t si = 0; si < n_seqs; ++si) {
+    std::vector<uint8_t> ps;
+    for (ograph::Handle h : g.paths[si].second) {
+      const auto& ns = g.seq[ograph::nid(h)];
+      if (ograph::isrev(h)) {
+        auto r = ograph::revcomp(ns);
+        ps.insert(ps.end(), r.begin(), r.end());
+      } else {
+        ps.insert(ps.end(), ns.begin(), ns.end());
+      }
+    }
+    if (ps.size() != seq_len[si] || memcmp(ps.data(), seq_data[si], ps.size()) != 0) return nullptr;
+  }
+  const std::string t = g.gfa();
+  char* out = (char*)malloc(t.size() + 1);
+  memcpy(out, t.c_str(), t.size() + 1);
+  return out;
+}
+extern "C" void orc_free(void* p) { free(p); }
+
+// ---------------------------------------------------------------------------
 // The pair-dispatch loop (src/seqrush.rs:611-757 with allwave/src/iterator.rs:185-203): one OS
 // thread per core instead of rayon, a thread-local aligner like allwave's thread_local
 // (allwave/src/alignment.rs:10-13). Used as the timed CPU baseline.

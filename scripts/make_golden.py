@@ -10,6 +10,7 @@ oracle/_ref built by `make -C oracle`). The outputs are committed; the GPU box o
       REFERENCE ITSELF (oracle/_ref = WFA2-lib + edlib compiled from /root/reference): orientation,
       both edit distances, raw score, run-length CIGAR. Covers 1 % / 5 % / 15 % divergence, long
       indels, N / lower-case bytes, whole-sequence RC, ragged lengths, 1-base and identical inputs.
+ 4. c1_gfa.npz : configs[0] as GFA from the restated builder / compaction / writer (see config1_gfa).
  3. DRB1-3123.fa.gz + c1_expected.json.gz : BASELINE.json configs[0] (HLA-zoo DRB1-3123, 12 seqs,
       -k 0): per ordered pair orientation / score / CIGAR digest from oracle/_ref, the unite-call
       count and a digest of the canonical partition from the restated glue.
@@ -173,8 +174,37 @@ def config1():
                                  "source": "oracle/_ref + oracle/oracle.cpp, scripts/make_golden.py"})
 
 
+def config1_gfa():
+    """BASELINE.json configs[0] as a GFA: the restated write_bidirected_gfa (oracle/oracle.cpp, literal
+    builder + compact + renumber + validate + write_gfa, --skip-sgd --skip-groom --skip-topo) over the
+    union-find the restated glue reaches when the 144 pairs are processed SEQUENTIALLY in the reference's
+    order (uf_rush roots depend on union order; this is the reference at -t 1). Stored: the compacted GFA text
+    (L lines sorted), the sha256 of the --no-compact text and the union-find root of every position, which is what
+    fixes the node bases (src/bidirected_builder.rs:176-182)."""
+    ids, seqs = load_fasta(os.path.join(REF, "HLA-zoo/seqs/DRB1-3123.fa"))
+    n = len(seqs)
+    pairs = np.array([(i, j) for i in range(n) for j in range(n)], dtype=np.uint32)
+    orc = _oracle.Oracle()
+    tot = int(sum(s.size for s in seqs))
+    uf = _oracle.OracleUF(tot)
+    uf.unite_fr_all(tot)
+    orc.run_pairs(seqs, pairs, min_match_len=0, threads=1, uf=uf, want_results=False)
+    raw, rep, nn = _oracle.build_gfa(uf, seqs, ids, no_compact=True)
+    gfa, _, _ = _oracle.build_gfa(uf, seqs, ids, no_compact=False)
+    np.savez_compressed(os.path.join(OUT, "c1_gfa.npz"), representatives=rep.astype(np.uint32),
+                        gfa=np.frombuffer(gfa.encode(), np.uint8),
+                        gfa_no_compact_sha256=np.frombuffer(hashlib.sha256(raw.encode()).hexdigest().encode(), np.uint8),
+                        uncompacted_nodes=np.array([nn], np.uint64))
+    print("wrote c1_gfa.npz", os.path.getsize(os.path.join(OUT, "c1_gfa.npz")), "bytes;", nn, "nodes before compaction,",
+          sum(1 for l in gfa.splitlines() if l.startswith("S")), "after; sha256", hashlib.sha256(gfa.encode()).hexdigest())
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
+    if len(sys.argv) > 1 and sys.argv[1] == "gfa":
+        config1_gfa()
+        sys.exit(0)
     wfa2_goldens()
     seqrush_pairs()
     config1()
+    config1_gfa()

@@ -9,9 +9,10 @@ from .allwave import (AlignmentParams, AlignmentResult, AllPairIterator, align_p
                       cigar_bytes_to_string, parse_scores, reverse_complement)
 from .allwave import Sequence as AllwaveSequence
 from .context import Context, default_context
+from .graph import BidirectedGraph, Handle
 from .seqrush import Args, SeqRush, Sequence, load_sequences
 from .union_find import BidirectedUnionFind
 
 __all__ = ["pos", "build", "SrgpuError", "AlignmentParams", "AlignmentResult", "AllPairIterator", "align_pair",
            "alignment_to_paf", "cigar_bytes_to_string", "parse_scores", "reverse_complement", "AllwaveSequence",
-           "Context", "default_context", "Args", "SeqRush", "Sequence", "load_sequences", "BidirectedUnionFind"]
+           "Context", "default_context", "BidirectedGraph", "Handle", "Args", "SeqRush", "Sequence", "load_sequences", "BidirectedUnionFind"]

@@ -4,8 +4,11 @@
 // device every entry point fails with SRGPU_E_CUDA.
 #include "../../include/seqrush_b200.h"
 #include "kernels.cuh"
+#include "graph.cuh"
+#include "graph_host.hpp"
 
 #include <algorithm>
+#include <functional>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -1173,3 +1176,265 @@ extern "C" int srgpu_uf_merge_roots(srgpu_uf* u, const void* d_peer_roots, uint6
   CK(cudaStreamSynchronize(c->stream));
   return SRGPU_OK;
 }
+
+// ---------------------------------------------------------------------------
+// Graph build from the partition (row f1): device passes (graph.cuh) + host compaction / writer
+// (graph_host.hpp). Reference: src/bidirected_builder.rs:17-289, src/bidirected_ops.rs:75-478,880-925,
+// src/bidirected_gfa_writer.rs:8-167 with --skip-sgd --skip-groom --skip-topo.
+// ---------------------------------------------------------------------------
+struct srgpu_graph {
+  HostGraph g;
+  std::vector<std::vector<uint8_t>> seq_copy;  // the input sequences (for validate_paths_match_sequences)
+  bool compacted = false;
+};
+
+extern "C" int srgpu_graph_build(srgpu_ctx* c, srgpu_uf* uf, const uint64_t* representatives, srgpu_graph** out) {
+  if (!c || !out) return SRGPU_E_ARG;
+  std::lock_guard<std::mutex> lk(c->mu);
+  CK(cudaSetDevice(c->device));
+  int rc;
+  if ((rc = check_uf(c, uf))) return rc;
+  const uint64_t n = c->total_len;
+  if (n == 0 || n > 0x7ffffff0ull) {
+    g_err = "graph build: empty sequence set or too many positions for 32-bit node handles";
+    return SRGPU_E_ARG;
+  }
+  DevBuf<uint32_t> d_comp, d_flag, d_rank, d_steps, d_bsum, d_first;
+  DevBuf<uint8_t> d_base;
+  DevBuf<unsigned long long> d_err, d_rep, d_keys, d_cnt;
+  DevBuf<uint2> d_edges;
+  struct Rel {
+    std::vector<std::function<void()>> f;
+    ~Rel() { for (auto& x : f) x(); }
+  } rel;
+#define GB(buf, cnt)                       \
+  if ((rc = (buf).ensure(cnt))) return rc; \
+  rel.f.push_back([&]() { (buf).release(); });
+  const uint64_t nblk = (n + SCAN_BLOCK - 1) / SCAN_BLOCK;
+  GB(d_comp, n) GB(d_flag, n) GB(d_rank, n) GB(d_steps, n) GB(d_bsum, nblk + 1) GB(d_err, 4) GB(d_cnt, 2)
+  if (representatives) {
+    GB(d_rep, n)
+    CK(cudaMemcpyAsync(d_rep.p, representatives, n * 8, cudaMemcpyHostToDevice, c->stream));
+  }
+  CK(cudaMemsetAsync(d_err.p, 0, 4 * 8, c->stream));
+  CK(cudaMemsetAsync(d_cnt.p, 0, 2 * 8, c->stream));
+  GraphArgs a;
+  a.seqs = seq_table(c);
+  a.parent = uf->parent.p;
+  a.total_len = n;
+  a.rep_in = representatives ? d_rep.p : nullptr;
+  a.comp = d_comp.p;
+  a.first_flag = d_flag.p;
+  a.rank = d_rank.p;
+  a.steps = d_steps.p;
+  a.node_base = nullptr;
+  a.err = d_err.p;
+  const int grid = grid_for(n, 256, c->n_sm);
+  graph_roots_kernel<<<grid, 256, 0, c->stream>>>(a);
+  CK(cudaGetLastError());
+  scan_block_sums_kernel<<<(unsigned)nblk, SCAN_THREADS, 0, c->stream>>>(d_flag.p, n, d_bsum.p);
+  CK(cudaGetLastError());
+  scan_sums_kernel<<<1, 1024, 0, c->stream>>>(d_bsum.p, nblk, d_cnt.p);
+  CK(cudaGetLastError());
+  scan_apply_kernel<<<(unsigned)nblk, SCAN_THREADS, 0, c->stream>>>(d_flag.p, n, d_bsum.p, d_rank.p);
+  CK(cudaGetLastError());
+  unsigned long long n_nodes = 0, errs[2] = {0, 0};
+  CK(cudaMemcpyAsync(&n_nodes, d_cnt.p, 8, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemcpyAsync(errs, d_err.p, 8, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  if (errs[0]) {
+    g_err = "graph build: " + std::to_string(errs[0]) + " positions whose forward and reverse Pos are not united "
+            "(the builder needs the invariant of SeqRush::new, src/seqrush.rs:324-328: call srgpu_uf_unite_fr_all first)";
+    return SRGPU_E_ARG;
+  }
+  GB(d_base, n_nodes + 1)
+  a.node_base = d_base.p;
+  graph_steps_kernel<<<grid, 256, 0, c->stream>>>(a);
+  CK(cudaGetLastError());
+  // edge set: open-addressing table of the canonical forms, first occurrence wins
+  uint64_t cap = 1024;
+  while (cap < 2 * n) cap <<= 1;
+  GB(d_keys, cap) GB(d_first, cap) GB(d_edges, n)
+  CK(cudaMemsetAsync(d_keys.p, 0xff, cap * 8, c->stream));
+  CK(cudaMemsetAsync(d_first.p, 0xff, cap * 4, c->stream));
+  EdgeArgs e;
+  e.seqs = a.seqs;
+  e.steps = d_steps.p;
+  e.total_len = n;
+  e.keys = d_keys.p;
+  e.first_at = d_first.p;
+  e.cap = cap;
+  e.out = d_edges.p;
+  e.n_out = d_cnt.p + 1;
+  graph_edges_insert_kernel<<<grid, 256, 0, c->stream>>>(e);
+  CK(cudaGetLastError());
+  graph_edges_collect_kernel<<<grid_for(cap, 256, c->n_sm), 256, 0, c->stream>>>(e);
+  CK(cudaGetLastError());
+  c->stats.kernel_launches += 7;
+  unsigned long long n_edges = 0;
+  CK(cudaMemcpyAsync(&n_edges, d_cnt.p + 1, 8, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemcpyAsync(errs, d_err.p, 16, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  if (errs[1]) {
+    g_err = "graph build: " + std::to_string(errs[1]) + " representatives lie outside the component of their position";
+    return SRGPU_E_ARG;
+  }
+  std::vector<uint8_t> h_base(n_nodes);
+  std::vector<uint32_t> h_steps(n);
+  std::vector<uint2> h_edges(n_edges);
+  if (n_nodes) CK(cudaMemcpy(h_base.data(), d_base.p, n_nodes, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(h_steps.data(), d_steps.p, n * 4, cudaMemcpyDeviceToHost));
+  if (n_edges) CK(cudaMemcpy(h_edges.data(), d_edges.p, n_edges * sizeof(uint2), cudaMemcpyDeviceToHost));
+  std::vector<uint8_t> h_fwd(c->d_fwd.n);
+  CK(cudaMemcpy(h_fwd.data(), c->d_fwd.p, c->d_fwd.n, cudaMemcpyDeviceToHost));
+  std::vector<uint64_t> h_boff(c->n_seqs);
+  CK(cudaMemcpy(h_boff.data(), c->d_byte_off.p, (size_t)c->n_seqs * 8, cudaMemcpyDeviceToHost));
+#undef GB
+  srgpu_graph* gr = new srgpu_graph();
+  HostGraph& g = gr->g;
+  g.seq.resize(n_nodes + 1);
+  g.present.assign(n_nodes + 1, 1);
+  g.present[0] = 0;
+  for (uint64_t i = 0; i < n_nodes; ++i) g.seq[i + 1].assign(1, (char)h_base[i]);
+  g.uncompacted_nodes = n_nodes;
+  g.edges.reserve(n_edges * 2);
+  for (const uint2& ed : h_edges) g.edges.insert(gedge(ed.x, ed.y));
+  g.paths.resize(c->n_seqs);
+  gr->seq_copy.resize(c->n_seqs);
+  for (uint32_t s = 0; s < c->n_seqs; ++s) {
+    const uint64_t o = c->h_pos_off[s], l = c->h_len[s];
+    g.paths[s].assign(h_steps.begin() + o, h_steps.begin() + o + l);
+    gr->seq_copy[s].assign(h_fwd.begin() + h_boff[s], h_fwd.begin() + h_boff[s] + l);
+  }
+  *out = gr;
+  return SRGPU_OK;
+}
+
+// The same object from caller-supplied parts (no device involved): the uncompacted graph as node bases,
+// per-path handle lists and stored edges. Lets a host keep its own builder and still use compact / validate /
+// write, and lets the CPU test-suite check those against the restated reference.
+extern "C" int srgpu_graph_from_parts(uint64_t n_nodes, const uint8_t* node_bases, uint32_t n_paths, const uint64_t* path_lens,
+                                      const uint64_t* steps, uint64_t n_edges, const uint64_t* from_to,
+                                      const srgpu_seqview* seqs, srgpu_graph** out) {
+  if (!out || (n_nodes && !node_bases) || (n_paths && (!path_lens || !steps || !seqs)) || (n_edges && !from_to)) return SRGPU_E_ARG;
+  srgpu_graph* gr = new srgpu_graph();
+  HostGraph& g = gr->g;
+  g.seq.resize(n_nodes + 1);
+  g.present.assign(n_nodes + 1, 1);
+  g.present[0] = 0;
+  for (uint64_t i = 0; i < n_nodes; ++i) g.seq[i + 1].assign(1, (char)node_bases[i]);
+  g.uncompacted_nodes = n_nodes;
+  for (uint64_t i = 0; i < n_edges; ++i) g.edges.insert(gedge((GHandle)from_to[2 * i], (GHandle)from_to[2 * i + 1]));
+  g.paths.resize(n_paths);
+  gr->seq_copy.resize(n_paths);
+  uint64_t at = 0;
+  for (uint32_t p = 0; p < n_paths; ++p) {
+    g.paths[p].resize(path_lens[p]);
+    for (uint64_t i = 0; i < path_lens[p]; ++i) {
+      const uint64_t h = steps[at + i];
+      if ((h >> 1) == 0 || (h >> 1) > n_nodes) {
+        delete gr;
+        g_err = "path step refers to a node that does not exist";
+        return SRGPU_E_ARG;
+      }
+      g.paths[p][i] = (GHandle)h;
+    }
+    at += path_lens[p];
+    gr->seq_copy[p].assign(seqs[p].data, seqs[p].data + seqs[p].len);
+  }
+  *out = gr;
+  return SRGPU_OK;
+}
+
+extern "C" int srgpu_graph_compact(srgpu_graph* gr) {
+  if (!gr) return SRGPU_E_ARG;
+  gr->g.compact();
+  gr->g.renumber();
+  gr->compacted = true;
+  return SRGPU_OK;
+}
+extern "C" uint64_t srgpu_graph_node_count(srgpu_graph* gr) { return gr ? gr->g.node_count() : 0; }
+extern "C" uint64_t srgpu_graph_edge_count(srgpu_graph* gr) { return gr ? gr->g.edges.size() : 0; }
+extern "C" uint64_t srgpu_graph_path_count(srgpu_graph* gr) { return gr ? gr->g.paths.size() : 0; }
+extern "C" uint64_t srgpu_graph_path_length(srgpu_graph* gr, uint32_t path) {
+  return (gr && path < gr->g.paths.size()) ? gr->g.paths[path].size() : 0;
+}
+extern "C" int srgpu_graph_path_steps(srgpu_graph* gr, uint32_t path, uint64_t* out, uint64_t cap) {
+  if (!gr || path >= gr->g.paths.size() || (!out && cap)) return SRGPU_E_ARG;
+  const auto& st = gr->g.paths[path];
+  for (uint64_t i = 0; i < st.size() && i < cap; ++i) out[i] = st[i];
+  return SRGPU_OK;
+}
+extern "C" int64_t srgpu_graph_node_sequence(srgpu_graph* gr, uint64_t node_id, char* buf, uint64_t cap) {
+  if (!gr || node_id >= gr->g.seq.size() || !gr->g.present[node_id]) return -1;
+  const std::string& s = gr->g.seq[node_id];
+  if (buf) memcpy(buf, s.data(), std::min<uint64_t>(cap, s.size()));
+  return (int64_t)s.size();
+}
+extern "C" int srgpu_graph_edges(srgpu_graph* gr, uint64_t* from_to, uint64_t cap_edges) {
+  if (!gr || (!from_to && cap_edges)) return SRGPU_E_ARG;
+  std::vector<uint64_t> es(gr->g.edges.begin(), gr->g.edges.end());
+  std::sort(es.begin(), es.end());
+  for (uint64_t i = 0; i < es.size() && i < cap_edges; ++i) {
+    from_to[2 * i] = es[i] >> 32;
+    from_to[2 * i + 1] = es[i] & 0xffffffffull;
+  }
+  return SRGPU_OK;
+}
+// validate_paths_match_sequences + write_gfa; *text is malloc'd (srgpu_free)
+extern "C" int srgpu_graph_gfa_text(srgpu_graph* gr, const char* const* names, uint32_t n_names, char** text, uint64_t* len) {
+  if (!gr || !names || !text || n_names != gr->g.paths.size()) return SRGPU_E_ARG;
+  std::vector<const uint8_t*> data(n_names);
+  std::vector<uint64_t> lens(n_names);
+  for (uint32_t i = 0; i < n_names; ++i) {
+    data[i] = gr->seq_copy[i].data();
+    lens[i] = gr->seq_copy[i].size();
+  }
+  const long bad = gr->g.validate(data, lens);
+  if (bad >= 0) {  // the reference returns Err("Path '<id>' does not match original sequence") and aborts the write
+    g_err = std::string("Path '") + names[bad] + "' does not match original sequence";
+    return SRGPU_E_INTERNAL;
+  }
+  std::vector<std::string> nm(n_names);
+  for (uint32_t i = 0; i < n_names; ++i) nm[i] = names[i] ? names[i] : "";
+  std::string t;
+  gr->g.gfa_text(nm, t);
+  char* o = (char*)malloc(t.size() + 1);
+  if (!o) {
+    g_err = "out of host memory for the GFA text";
+    return SRGPU_E_INTERNAL;
+  }
+  memcpy(o, t.c_str(), t.size() + 1);
+  *text = o;
+  if (len) *len = t.size();
+  return SRGPU_OK;
+}
+extern "C" int srgpu_graph_write_gfa(srgpu_graph* gr, const char* const* names, uint32_t n_names, const char* path) {
+  if (!path) return SRGPU_E_ARG;
+  char* t = nullptr;
+  uint64_t n = 0;
+  const int rc = srgpu_graph_gfa_text(gr, names, n_names, &t, &n);
+  if (rc) return rc;
+  FILE* f = fopen(path, "wb");
+  if (!f) {
+    free(t);
+    g_err = std::string("cannot create ") + path;
+    return SRGPU_E_ARG;
+  }
+  const size_t w = fwrite(t, 1, n, f);
+  fclose(f);
+  free(t);
+  if (w != n) {
+    g_err = "short write";
+    return SRGPU_E_INTERNAL;
+  }
+  return SRGPU_OK;
+}
+extern "C" int srgpu_graph_stats(srgpu_graph* gr, uint64_t* uncompacted_nodes, uint32_t* rounds, uint32_t* merged_chains) {
+  if (!gr) return SRGPU_E_ARG;
+  if (uncompacted_nodes) *uncompacted_nodes = gr->g.uncompacted_nodes;
+  if (rounds) *rounds = gr->g.rounds;
+  if (merged_chains) *merged_chains = gr->g.merged_chains;
+  return SRGPU_OK;
+}
+extern "C" void srgpu_graph_free(srgpu_graph* gr) { delete gr; }

@@ -238,6 +238,19 @@ class SeqRush:
                 "random_pairs_processed": done, "random_pairs_skipped": len(random_pairs) - done,
                 "stabilized": stabilized}
 
+    def build_bidirected_graph(self, representatives=None):  # src/bidirected_builder.rs:17-289
+        from .graph import build_bidirected_graph
+        return build_bidirected_graph(self, representatives)
+
+    def write_bidirected_gfa(self, output_path: str, no_compact: bool = False, representatives=None):
+        """src/bidirected_gfa_writer.rs:8-167 with --skip-sgd --skip-groom --skip-topo: build, compact and
+        renumber unless no_compact, validate the paths against the sequences, write. Returns the graph."""
+        g = self.build_bidirected_graph(representatives)
+        if not no_compact:
+            g.compact()
+        g.write_gfa(output_path)
+        return g
+
     def count_components(self) -> int:  # :341-353
         return self.union_find.count_components(self.total_length)
 

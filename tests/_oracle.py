@@ -75,6 +75,9 @@ def lib():
     L.orc_process_alignment.argtypes = [vp, C.c_char_p, vp, u64, u64, vp, u64, u64, u64, i32, u64, u64]
     L.orc_run_pairs.argtypes = [vp, vp, vp, vp, C.c_uint32, vp, u64, C.POINTER(i32), u64, i32, vp, C.POINTER(RunStats)]
     L.orc_swg2p_penalty.argtypes = [vp, i32, vp, i32, C.POINTER(i32)]
+    L.orc_build_gfa.restype = vp
+    L.orc_build_gfa.argtypes = [vp, vp, vp, C.c_uint32, vp, i32, vp, C.POINTER(u64)]
+    L.orc_free.argtypes = [vp]
     _lib = L
     return L
 
@@ -179,6 +182,24 @@ class OracleUF:
         a, b = Oracle._arr(d1), Oracle._arr(d2)
         return lib().orc_process_alignment(self.h, cigar.encode(), a.ctypes.data, a.size, o1, b.ctypes.data, b.size,
                                            o2, min_match_len, int(bool(query_is_rc)), qstart, tstart)
+
+
+def build_gfa(uf, seqs, ids, no_compact=False):
+    """Restated write_bidirected_gfa (--skip-sgd --skip-groom --skip-topo): build from the union-find,
+    compact + renumber unless no_compact, validate, write (L lines sorted).
+    Returns (gfa text, representative Pos of every position = what fixes the node bases, #nodes before compaction)."""
+    arrs = [Oracle._arr(s) for s in seqs]
+    ptrs = (C.c_void_p * len(arrs))(*[a.ctypes.data for a in arrs])
+    lens = np.array([a.size for a in arrs], dtype=np.uint64)
+    names = (C.c_char_p * len(ids))(*[i.encode() for i in ids])
+    rep = np.zeros(int(lens.sum()), dtype=np.uint64)
+    nn = C.c_uint64()
+    p = lib().orc_build_gfa(uf.h, ptrs, lens.ctypes.data, len(arrs), names, int(bool(no_compact)), rep.ctypes.data, C.byref(nn))
+    if not p:
+        raise RuntimeError("oracle: path validation failed (validate_paths_match_sequences)")
+    txt = C.string_at(p).decode()
+    lib().orc_free(p)
+    return txt, rep, nn.value
 
 
 def swg2p_penalty(p, t, pen=(5, 8, 2, 24, 1)):

@@ -400,3 +400,98 @@ def test_iterative_early_stop(s, oracle):
     assert out["final_components"] == ouf.count_components(sr.total_length)
     assert np.array_equal(sr.canonical_partition(), ouf.canonical(2 * sr.total_length))
     ctx.close()
+
+
+def _gfa_flip_normalise(txt_ours, txt_ref):
+    """--no-compact GFAs of the same partition differ only by the orientation of nodes whose base the two
+    sides read from different members of a mixed-orientation component: flip those nodes in `txt_ref`
+    (complement the base, toggle the sign of every step and edge end) and return the re-sorted text."""
+    comp = {"A": "T", "T": "A", "C": "G", "G": "C"}
+    base_ours = {f[1]: f[2] for f in (l.split("\t") for l in txt_ours.splitlines()) if f[0] == "S"}
+    flip = set()
+    out, links = [], []
+    for l in txt_ref.splitlines():
+        f = l.split("\t")
+        if f[0] == "S":
+            if base_ours[f[1]] != f[2]:
+                assert comp.get(f[2].upper()) == base_ours[f[1]].upper(), (f, base_ours[f[1]])
+                flip.add(f[1])
+                f[2] = base_ours[f[1]]
+            out.append("\t".join(f))
+        elif f[0] == "L":
+            a, b = (f[1], f[2]), (f[3], f[4])
+            a = (a[0], "-" if (a[1] == "+") == (a[0] in flip) else "+") if a[0] in flip else a
+            b = (b[0], "-" if (b[1] == "+") == (b[0] in flip) else "+") if b[0] in flip else b
+            links.append((a, b))
+        elif f[0] == "P":
+            steps = [(x[:-1], x[-1]) for x in f[2].split(",")]
+            steps = [(n, ("-" if o == "+" else "+") if n in flip else o) for n, o in steps]
+            out.append("P\t%s\t%s\t*" % (f[1], ",".join(n + o for n, o in steps)))
+        else:
+            out.append(l)
+    return out, links, flip
+
+
+def test_graph_build_and_gfa(s, oracle, c1_golden):
+    """Row f1: srgpu_graph_build (device: roots, first-seen numbering, steps, edge set) + compaction + GFA
+    writer against the restated reference (oracle/oracle.cpp) on the GPU's own partition.
+      * forward-only set: byte-identical GFA, --no-compact and compacted, with the library's own representatives;
+      * set with reverse-complemented sequences: byte-identical once the builder is given the sequential uf_rush
+        roots as representatives; with its own representatives the --no-compact graph is the same up to the
+        orientation of mixed-component nodes;
+      * BASELINE.json configs[0] (HLA DRB1-3123, 22 RC pairs): byte-identical to the committed reference GFA."""
+    import _oracle
+    from seqrush_b200 import synth
+    from test_graph_host import oracle_partition
+    for cfg, mixed in (((6, 3000, 0.02, 41, 0.0, 0.0), False), ((7, 2500, 0.03, 42, 0.45, 0.3), True)):
+        ids, seqs = synth.make_sequences(*cfg)
+        ctx = s.Context(0)
+        sr = s.SeqRush([s.Sequence(i, a.tobytes()) for i, a in zip(ids, seqs)], ctx=ctx)
+        sr.align_and_unite(s.Args(min_match_length=0))
+        uf = oracle_partition(oracle, seqs)
+        assert np.array_equal(sr.canonical_partition(), uf.canonical(2 * sr.total_length))
+        raw, rep, nn = _oracle.build_gfa(uf, seqs, ids, no_compact=True)
+        want, _, _ = _oracle.build_gfa(uf, seqs, ids, no_compact=False)
+        g = sr.build_bidirected_graph(representatives=rep)
+        assert g.stats()["uncompacted_nodes"] == nn and g.node_count == nn
+        assert g.gfa_text() == raw
+        assert g.compact().gfa_text() == want
+        g.close()
+        g = sr.build_bidirected_graph()  # the library's canonical representatives
+        mine = g.gfa_text()
+        if not mixed:
+            assert mine == raw and g.compact().gfa_text() == want
+        else:
+            out, links, flip = _gfa_flip_normalise(mine, raw)
+            assert flip, "the set has mixed-orientation components"
+            mine_l = [l for l in mine.splitlines() if not l.startswith("L")]
+            assert mine_l == out
+            canon = lambda a, b: min((a, b), ((b[0], "-" if b[1] == "+" else "+"), (a[0], "-" if a[1] == "+" else "+")))
+            mine_links = sorted(canon((f[1], f[2]), (f[3], f[4])) for f in (l.split("\t") for l in mine.splitlines()) if f[0] == "L")
+            assert mine_links == sorted(canon(a, b) for a, b in links)
+            first = {}
+            for p in range(len(ids)):  # first step through every node is '+'
+                for h in g.path(p):
+                    first.setdefault(h.node_id, h.is_reverse)
+            assert not any(first.values())
+        g.close()
+        ctx.close()
+    # configs[0]
+    import hashlib
+    import os
+    from conftest import GOLDEN
+    exp, ids, seqs = c1_golden
+    z = np.load(os.path.join(GOLDEN, "c1_gfa.npz"))
+    ctx = s.Context(0)
+    sr = s.SeqRush([s.Sequence(i, d) for i, d in zip(ids, seqs)], ctx=ctx)
+    sr.align_and_unite(s.Args(min_match_length=0))
+    g = sr.build_bidirected_graph(representatives=z["representatives"].astype(np.uint64))
+    assert g.node_count == int(z["uncompacted_nodes"][0])
+    assert hashlib.sha256(g.gfa_text().encode()).hexdigest() == bytes(z["gfa_no_compact_sha256"]).decode()
+    g.compact()
+    assert g.gfa_text() == bytes(z["gfa"]).decode()
+    out = sr.write_bidirected_gfa(os.path.join(os.environ.get("TMPDIR", "/tmp"), "c1_own.gfa"))  # own representatives
+    assert out.node_count > 0 and out.stats()["uncompacted_nodes"] == int(z["uncompacted_nodes"][0])
+    out.close()
+    g.close()
+    ctx.close()
