@@ -42,8 +42,15 @@ typedef struct {
   uint64_t len;
 } srgpu_seqview;
 
-/* Reference: allwave::AlignmentParams (allwave/src/types.rs:37-46); match must be 0 and the
- * two-piece penalties present (AlignmentMode::TwoPieceAffine, types.rs:101-111). */
+/* Reference: allwave::AlignmentParams (allwave/src/types.rs:37-46) in any of allwave's modes
+ * (AlignmentMode::from_params, types.rs:101-111; allwave/src/alignment.rs:203-231):
+ *   two-piece affine    gap_ext2 > 0;
+ *   single-piece affine gap_open2 / gap_ext2 <= 0 (the Option is None): the gap-affine BiWFA;
+ *   "edit distance"     the same with gap_open1 == gap_ext1 == mismatch (allwave runs it as affine x,x,x).
+ * match_score follows WFA2-lib: 0, or negative with Eizenga's adjustment of the other penalties
+ * (WFA2-lib/wavefront/wavefront_penalties.c:113-134,157-175; the score reported is then
+ * (|match| * (qlen + tlen) - wf_score) / 2, wavefront_compute.c:108-120). A positive match score is refused with
+ * SRGPU_E_ARG and WFA2-lib's message: WFA2-lib itself prints it and exits (:100-103,141-144). */
 typedef struct {
   int32_t match_score;
   int32_t mismatch;
@@ -206,6 +213,25 @@ int srgpu_uf_merge_roots(srgpu_uf* uf, const void* d_peer_roots, uint64_t n);
  * that unites (p, gathered[r][p]) for every peer r != my_rank. */
 int srgpu_uf_compress_async(srgpu_uf* uf);
 int srgpu_uf_merge_gathered(srgpu_uf* uf, const void* d_gathered, uint64_t n, int world, int my_rank);
+
+/* ---- Pair-list sparsification (allwave::SparsificationStrategy, allwave/src/types.rs:64-80; flag parsing
+ * src/seqrush.rs:356-431). The reference derives sparsified pair lists from Rust's DefaultHasher (SipHash-1-3 with
+ * zero keys): MinHash sketches of canonical k-mer hashes (allwave/src/mash.rs:78-107: `[u8]` framing = u64 LE length,
+ * then the bytes), Mash distances, k-nearest / k-farthest neighbours (allwave/src/knn_graph.rs:10-142) and a hashed
+ * filter on the String "{id_i}:{id_j}" (`str` framing = bytes, then 0xff; allwave/src/iterator.rs:256-284,
+ * knn_graph.rs:145-172). The hashing, the sketch selection and the n^2 Jaccard counts run on the device; the host
+ * turns the integer counts into distances and neighbour lists (seqrush_b200/sparsify.py). ---- */
+uint64_t srgpu_rust_hash_bytes(const uint8_t* data, uint64_t n); /* DefaultHasher::new(); data.hash(); finish() for &[u8] */
+uint64_t srgpu_rust_hash_str(const char* s);                     /* the same for a String / &str */
+/* Sketches of the uploaded sequences (sketch_size smallest canonical k-mer hashes each, ascending, duplicates kept:
+ * sketches_out[n][sketch_size], counts_out[n]) and, for every sequence pair, the sizes of the intersection and of the
+ * union of the two sketches as sets (inter_out[n][n], uni_out[n][n], symmetric, diagonal 0). Outputs may be NULL. */
+int srgpu_mash_sketch_jaccard(srgpu_ctx* ctx, uint32_t kmer_size, uint32_t sketch_size, uint64_t* sketches_out,
+                              uint32_t* counts_out, uint32_t* inter_out, uint32_t* uni_out);
+/* keep_out[i*n+j] = 1 when hash("{ids[i]}:{ids[j]}") / 2^64 < fraction (and i != j when exclude_self);
+ * hashes_out (optional) receives the n*n hash values. */
+int srgpu_pair_hash_filter(srgpu_ctx* ctx, const char* const* ids, uint32_t n, double fraction, int exclude_self,
+                           uint8_t* keep_out, uint64_t* hashes_out);
 
 /* ---- Graph build from the partition (the consumer of the union-find): the reference's
  * write_bidirected_gfa (src/bidirected_gfa_writer.rs:8-167) with --skip-sgd --skip-groom --skip-topo =

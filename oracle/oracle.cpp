@@ -18,6 +18,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <math.h>
 #include <atomic>
 #include <string>
 #include <thread>
@@ -134,6 +135,18 @@ extern "C" int orc_wfa_only(void* h, const uint8_t* p, int plen, const uint8_t* 
                             int memory_mode, char* cigar_out, int* cigar_len, int* score) {
   Oracle* o = (Oracle*)h;
   void* wf = o->wfa_new(pen5[0], pen5[1], pen5[2], pen5[3], pen5[4], memory_mode);
+  const int st = o->wfa_align(wf, (const char*)p, plen, (const char*)t, tlen, cigar_out, cigar_len, score);
+  o->wfa_free(wf);
+  return st;
+}
+// the same for any of allwave's modes (allwave/src/alignment.rs:203-231): pen6 = match (<= 0), x, o1, e1, o2, e2
+typedef void* (*fn_wfa_new_mode)(int, int, int, int, int, int, int, int);
+extern "C" int orc_wfa_mode(void* h, const uint8_t* p, int plen, const uint8_t* t, int tlen, const int* pen6, int two_piece,
+                            char* cigar_out, int* cigar_len, int* score) {
+  Oracle* o = (Oracle*)h;
+  fn_wfa_new_mode mk = (fn_wfa_new_mode)dlsym(o->dl, "ref_wfa_new_mode");
+  if (!mk) return -100;
+  void* wf = mk(pen6[0], pen6[1], pen6[2], pen6[3], pen6[4], pen6[5], two_piece, 3);
   const int st = o->wfa_align(wf, (const char*)p, plen, (const char*)t, tlen, cigar_out, cigar_len, score);
   o->wfa_free(wf);
   return st;
@@ -813,6 +826,197 @@ extern "C" char* orc_build_gfa(void* u, const uint8_t* const* seq_data, const ui
   return out;
 }
 extern "C" void orc_free(void* p) { free(p); }
+
+// ---------------------------------------------------------------------------
+// Pair-list sparsification (allwave/src/iterator.rs:49-77,256-284; allwave/src/mash.rs:30-165;
+// allwave/src/knn_graph.rs:10-172). Everything hashes through Rust's
+// std::collections::hash_map::DefaultHasher = SipHash-1-3 with zero keys (std source is not in the
+// reference tree; restated from the published SipHash definition, Aumasson & Bernstein 2012, with
+// c = 1 compression round and d = 3 finalisation rounds). Framing of the hashed bytes as in Rust's
+// `Hash` impls: `[u8]` writes the length as a little-endian u64 and then the bytes; `str`/`String`
+// writes the bytes and then one 0xff byte. PARITY UNPINNED for the framing: no reference test holds a
+// hash value or a pair list (allwave/src/knn_graph.rs:198-384 asserts counts and ranges only); the
+// SipHash core is pinned by the published SipHash-2-4 vector and the SipHash-1-3 vectors of Rust's
+// own test-suite (tests/test_sparsify.py).
+// ---------------------------------------------------------------------------
+static inline uint64_t rotl64(uint64_t x, int b) { return (x << b) | (x >> (64 - b)); }
+static uint64_t siphash(const uint8_t* in, size_t len, uint64_t k0, uint64_t k1, int c_rounds, int d_rounds) {
+  uint64_t v0 = 0x736f6d6570736575ull ^ k0, v1 = 0x646f72616e646f6dull ^ k1, v2 = 0x6c7967656e657261ull ^ k0,
+           v3 = 0x7465646279746573ull ^ k1;
+  auto round = [&]() {
+    v0 += v1; v1 = rotl64(v1, 13); v1 ^= v0; v0 = rotl64(v0, 32);
+    v2 += v3; v3 = rotl64(v3, 16); v3 ^= v2;
+    v0 += v3; v3 = rotl64(v3, 21); v3 ^= v0;
+    v2 += v1; v1 = rotl64(v1, 17); v1 ^= v2; v2 = rotl64(v2, 32);
+  };
+  const size_t nw = len / 8;
+  for (size_t w = 0; w < nw; ++w) {
+    uint64_t m = 0;
+    for (int i = 0; i < 8; ++i) m |= (uint64_t)in[8 * w + i] << (8 * i);
+    v3 ^= m;
+    for (int r = 0; r < c_rounds; ++r) round();
+    v0 ^= m;
+  }
+  uint64_t b = (uint64_t)(len & 0xff) << 56;
+  for (size_t i = 0; i < (len & 7); ++i) b |= (uint64_t)in[8 * nw + i] << (8 * i);
+  v3 ^= b;
+  for (int r = 0; r < c_rounds; ++r) round();
+  v0 ^= b;
+  v2 ^= 0xff;
+  for (int r = 0; r < d_rounds; ++r) round();
+  return v0 ^ v1 ^ v2 ^ v3;
+}
+extern "C" uint64_t orc_siphash(const uint8_t* in, uint64_t len, uint64_t k0, uint64_t k1, int c_rounds, int d_rounds) {
+  return siphash(in, (size_t)len, k0, k1, c_rounds, d_rounds);
+}
+// DefaultHasher over a `&[u8]` (Hash for [u8]: length prefix, then the bytes) and over a `String`
+static uint64_t rust_hash_bytes(const uint8_t* b, size_t n) {
+  std::vector<uint8_t> buf(8 + n);
+  for (int i = 0; i < 8; ++i) buf[i] = (uint8_t)((uint64_t)n >> (8 * i));
+  memcpy(buf.data() + 8, b, n);
+  return siphash(buf.data(), buf.size(), 0, 0, 1, 3);
+}
+static uint64_t rust_hash_str(const std::string& s) {
+  std::vector<uint8_t> buf(s.begin(), s.end());
+  buf.push_back(0xff);
+  return siphash(buf.data(), buf.size(), 0, 0, 1, 3);
+}
+extern "C" uint64_t orc_rust_hash_bytes(const uint8_t* b, uint64_t n) { return rust_hash_bytes(b, (size_t)n); }
+extern "C" uint64_t orc_rust_hash_str(const char* s) { return rust_hash_str(std::string(s)); }
+
+// sketch_sequence (allwave/src/mash.rs:78-107): every k-mer without a non-ACGT byte, canonical = the smaller
+// of the two HASHES, sorted, truncated to sketch_size (duplicates are kept). Returns the count written.
+static bool is_dna_base(uint8_t b) {
+  if (b >= 'a' && b <= 'z') b -= 32;
+  return b == 'A' || b == 'C' || b == 'G' || b == 'T';
+}
+static std::vector<uint64_t> sketch_sequence(const uint8_t* s, size_t n, size_t k, size_t sketch_size) {
+  std::vector<uint64_t> hashes;
+  if (n < k) return hashes;
+  std::vector<uint8_t> rc(k);
+  for (size_t i = 0; i + k <= n; ++i) {
+    bool ok = true;
+    for (size_t j = 0; j < k; ++j)
+      if (!is_dna_base(s[i + j])) {
+        ok = false;
+        break;
+      }
+    if (!ok) continue;
+    for (size_t j = 0; j < k; ++j) {  // reverse_complement_kmer, :124-136
+      uint8_t b = s[i + k - 1 - j], u = (b >= 'a' && b <= 'z') ? (uint8_t)(b - 32) : b;
+      rc[j] = u == 'A' ? 'T' : u == 'T' ? 'A' : u == 'C' ? 'G' : u == 'G' ? 'C' : b;
+    }
+    const uint64_t hf = rust_hash_bytes(s + i, k), hr = rust_hash_bytes(rc.data(), k);
+    hashes.push_back(hf < hr ? hf : hr);
+  }
+  std::sort(hashes.begin(), hashes.end());
+  if (hashes.size() > sketch_size) hashes.resize(sketch_size);
+  return hashes;
+}
+extern "C" uint64_t orc_sketch(const uint8_t* s, uint64_t n, uint64_t k, uint64_t sketch_size, uint64_t* out) {
+  const std::vector<uint64_t> h = sketch_sequence(s, (size_t)n, (size_t)k, (size_t)sketch_size);
+  memcpy(out, h.data(), h.size() * 8);
+  return h.size();
+}
+// KmerSketch::jaccard + mash_distance (:40-73)
+static double mash_distance(const std::vector<uint64_t>& a, const std::vector<uint64_t>& b, size_t k, uint64_t* inter_out,
+                            uint64_t* uni_out) {
+  std::set<uint64_t> s1(a.begin(), a.end()), s2(b.begin(), b.end());
+  uint64_t inter = 0;
+  for (uint64_t x : s1) inter += s2.count(x);
+  const uint64_t uni = s1.size() + s2.size() - inter;
+  if (inter_out) *inter_out = inter;
+  if (uni_out) *uni_out = uni;
+  const double jac = uni == 0 ? 0.0 : (double)inter / (double)uni;
+  if (jac <= 0.0) return 1.0;
+  const double ratio = (2.0 * jac) / (1.0 + jac);
+  if (ratio <= 0.0) return 1.0;
+  return (-1.0 / (double)k) * log(ratio);
+}
+static bool should_include_pair(const std::string& a, const std::string& b, double fraction) {  // knn_graph.rs:159-172
+  const uint64_t h = rust_hash_str(a + ":" + b);
+  const double normalized = (double)h / 18446744073709551615.0;  // u64::MAX as f64 == 2^64
+  return normalized < fraction;
+}
+// extract_tree_pairs / extract_tree_pairs_separated (knn_graph.rs:10-97). pairs_out gets up to cap (i, j) pairs;
+// returns the number of pairs (tree pairs first when `separated`, *n_tree = their count).
+extern "C" uint64_t orc_tree_pairs(const uint8_t* const* seq_data, const uint64_t* seq_len, const char* const* ids, uint32_t n,
+                                   uint64_t k_nearest, uint64_t k_farthest, double random_fraction, uint64_t kmer_size,
+                                   int separated, uint32_t* pairs_out, uint64_t cap, uint64_t* n_tree, double* dist_out) {
+  typedef std::pair<uint64_t, uint64_t> P;
+  std::vector<P> tree, rnd;
+  if (n_tree) *n_tree = 0;
+  if (n < 2) return 0;
+  std::vector<std::vector<uint64_t>> sk(n);
+  for (uint32_t i = 0; i < n; ++i) sk[i] = sketch_sequence(seq_data[i], (size_t)seq_len[i], (size_t)kmer_size, 1000);
+  std::vector<std::vector<double>> d(n, std::vector<double>(n, 0.0));
+  for (uint32_t i = 0; i < n; ++i)
+    for (uint32_t j = i + 1; j < n; ++j) d[i][j] = d[j][i] = mash_distance(sk[i], sk[j], (size_t)kmer_size, nullptr, nullptr);
+  if (dist_out)
+    for (uint32_t i = 0; i < n; ++i)
+      for (uint32_t j = 0; j < n; ++j) dist_out[(size_t)i * n + j] = d[i][j];
+  auto knn = [&](uint64_t kk, bool farthest) {  // build_knn_graph, :110-142 (sort_by is stable)
+    for (uint32_t i = 0; i < n; ++i) {
+      std::vector<std::pair<double, uint64_t>> nb;
+      for (uint32_t j = 0; j < n; ++j)
+        if (j != i) nb.emplace_back(d[i][j], j);
+      if (farthest) std::stable_sort(nb.begin(), nb.end(), [](const auto& a, const auto& b) { return a.first > b.first; });
+      else std::stable_sort(nb.begin(), nb.end(), [](const auto& a, const auto& b) { return a.first < b.first; });
+      for (uint64_t t = 0; t < kk && t < nb.size(); ++t) tree.emplace_back(i, nb[t].second);
+    }
+  };
+  if (k_nearest > 0) knn(k_nearest, false);
+  if (k_farthest > 0) knn(k_farthest, true);
+  if (random_fraction > 0.0)
+    for (uint32_t i = 0; i < n; ++i)
+      for (uint32_t j = 0; j < n; ++j)
+        if (i != j && should_include_pair(ids[i], ids[j], random_fraction)) rnd.emplace_back(i, j);
+  std::vector<P> out;
+  if (!separated) {
+    tree.insert(tree.end(), rnd.begin(), rnd.end());
+    std::sort(tree.begin(), tree.end());
+    tree.erase(std::unique(tree.begin(), tree.end()), tree.end());
+    out = tree;
+    if (n_tree) *n_tree = out.size();
+  } else {
+    std::sort(tree.begin(), tree.end());
+    tree.erase(std::unique(tree.begin(), tree.end()), tree.end());
+    out = tree;
+    if (n_tree) *n_tree = tree.size();
+    for (const P& p : rnd)
+      if (!std::binary_search(tree.begin(), tree.end(), p)) out.push_back(p);
+  }
+  for (size_t i = 0; i < out.size() && i < cap; ++i) {
+    pairs_out[2 * i] = (uint32_t)out[i].first;
+    pairs_out[2 * i + 1] = (uint32_t)out[i].second;
+  }
+  return out.size();
+}
+// apply_random_sparsification (iterator.rs:256-284) over the n^2 (or n^2 - n) i-major pair list
+extern "C" uint64_t orc_random_pairs(const char* const* ids, uint32_t n, int exclude_self, double keep_fraction,
+                                     uint32_t* pairs_out, uint64_t cap) {
+  uint64_t m = 0;
+  for (uint32_t i = 0; i < n; ++i)
+    for (uint32_t j = 0; j < n; ++j) {
+      if (exclude_self && i == j) continue;
+      if (should_include_pair(ids[i], ids[j], keep_fraction)) {
+        if (m < cap) {
+          pairs_out[2 * m] = i;
+          pairs_out[2 * m + 1] = j;
+        }
+        ++m;
+      }
+    }
+  return m;
+}
+// compute_connectivity_probability (iterator.rs:300-334)
+extern "C" double orc_connectivity_probability(uint64_t n, double connectivity_prob) {
+  if (n <= 1) return 1.0;
+  double x = connectivity_prob < 0.001 ? 0.001 : connectivity_prob > 0.999 ? 0.999 : connectivity_prob;
+  if (n <= 10) return n == 2 ? 1.0 : n == 3 ? 0.8 : n == 4 ? 0.7 : n == 5 ? 0.6 : 0.5;
+  const double nf = (double)n, c = -log(-log(x)), p = (log(nf) + c) / nf;
+  return p < 0.001 ? 0.001 : p > 1.0 ? 1.0 : p;
+}
 
 // ---------------------------------------------------------------------------
 // The pair-dispatch loop (src/seqrush.rs:611-757 with allwave/src/iterator.rs:185-203): one OS

@@ -43,6 +43,34 @@ void* ref_wfa_new(int mismatch, int o1, int e1, int o2, int e2, int memory_mode)
   h->wf = wavefront_aligner_new(&attr);
   return h;
 }
+/* Any of allwave's three modes (allwave/src/alignment.rs:203-231): two_piece = 1 -> gap-affine-2p, 0 -> gap-affine
+ * (single piece; allwave's "edit distance" mode is this with o = e = x). match <= 0 (WFA2-lib exits on match > 0,
+ * wavefront/wavefront_penalties.c:100-103). */
+void* ref_wfa_new_mode(int match, int mismatch, int o1, int e1, int o2, int e2, int two_piece, int memory_mode) {
+  wavefront_aligner_attr_t attr = wavefront_aligner_attr_default;
+  if (two_piece) {
+    attr.distance_metric = gap_affine_2p;
+    attr.affine2p_penalties.match = match;
+    attr.affine2p_penalties.mismatch = mismatch;
+    attr.affine2p_penalties.gap_opening1 = o1;
+    attr.affine2p_penalties.gap_extension1 = e1;
+    attr.affine2p_penalties.gap_opening2 = o2;
+    attr.affine2p_penalties.gap_extension2 = e2;
+  } else {
+    attr.distance_metric = gap_affine;
+    attr.affine_penalties.match = match;
+    attr.affine_penalties.mismatch = mismatch;
+    attr.affine_penalties.gap_opening = o1;
+    attr.affine_penalties.gap_extension = e1;
+  }
+  attr.alignment_scope = compute_alignment;
+  attr.alignment_form.span = alignment_end2end;
+  attr.heuristic.strategy = wf_heuristic_none;
+  attr.memory_mode = (memory_mode == 3) ? wavefront_memory_ultralow : wavefront_memory_high;
+  ref_wfa_t* h = (ref_wfa_t*)calloc(1, sizeof(ref_wfa_t));
+  h->wf = wavefront_aligner_new(&attr);
+  return h;
+}
 void ref_wfa_free(void* hv) {
   ref_wfa_t* h = (ref_wfa_t*)hv;
   if (!h) return;

@@ -8,11 +8,14 @@ from ._lib import build, SrgpuError
 from .allwave import (AlignmentParams, AlignmentResult, AllPairIterator, align_pair, alignment_to_paf,
                       cigar_bytes_to_string, parse_scores, reverse_complement)
 from .allwave import Sequence as AllwaveSequence
+from .aligner import (Aligner, AlignerBackend, AlignmentRecord, AlignmentSequence, AllwaveAligner, create_aligner)
 from .context import Context, default_context
 from .graph import BidirectedGraph, Handle
+from .sparsify import SparsificationStrategy, parse_sparsification
 from .seqrush import Args, SeqRush, Sequence, load_sequences
 from .union_find import BidirectedUnionFind
 
 __all__ = ["pos", "build", "SrgpuError", "AlignmentParams", "AlignmentResult", "AllPairIterator", "align_pair",
            "alignment_to_paf", "cigar_bytes_to_string", "parse_scores", "reverse_complement", "AllwaveSequence",
-           "Context", "default_context", "BidirectedGraph", "Handle", "Args", "SeqRush", "Sequence", "load_sequences", "BidirectedUnionFind"]
+           "Aligner", "AlignerBackend", "AlignmentRecord", "AlignmentSequence", "AllwaveAligner", "create_aligner",
+           "Context", "default_context", "BidirectedGraph", "Handle", "SparsificationStrategy", "parse_sparsification", "Args", "SeqRush", "Sequence", "load_sequences", "BidirectedUnionFind"]

@@ -26,6 +26,7 @@ EXPORTS = [
     "srgpu_uf_unite_matching_region", "srgpu_uf_unite_matching_region_seq2_rc", "srgpu_uf_unite_regions",
     "srgpu_uf_unite_fr_all", "srgpu_uf_roots", "srgpu_uf_count_components", "srgpu_uf_checksum",
     "srgpu_uf_device_ptr", "srgpu_uf_compress", "srgpu_uf_merge_roots",
+    "srgpu_rust_hash_bytes", "srgpu_rust_hash_str", "srgpu_mash_sketch_jaccard", "srgpu_pair_hash_filter",
     "srgpu_graph_build", "srgpu_graph_from_parts", "srgpu_graph_compact", "srgpu_graph_node_count", "srgpu_graph_edge_count",
     "srgpu_graph_path_count", "srgpu_graph_path_length", "srgpu_graph_path_steps", "srgpu_graph_node_sequence",
     "srgpu_graph_edges", "srgpu_graph_gfa_text", "srgpu_graph_write_gfa", "srgpu_graph_stats", "srgpu_graph_free",
@@ -151,6 +152,12 @@ def lib():
     L.srgpu_uf_merge_gathered.argtypes = [vp, vp, u64, i32, i32]
     L.srgpu_ctx_stream.argtypes = [vp]
     L.srgpu_ctx_stream.restype = vp
+    L.srgpu_rust_hash_bytes.argtypes = [vp, u64]
+    L.srgpu_rust_hash_bytes.restype = u64
+    L.srgpu_rust_hash_str.argtypes = [C.c_char_p]
+    L.srgpu_rust_hash_str.restype = u64
+    L.srgpu_mash_sketch_jaccard.argtypes = [vp, u32, u32, vp, vp, vp, vp]
+    L.srgpu_pair_hash_filter.argtypes = [vp, vp, u32, C.c_double, i32, vp, vp]
     L.srgpu_graph_build.argtypes = [vp, vp, vp, C.POINTER(vp)]
     L.srgpu_graph_from_parts.argtypes = [u64, vp, u32, vp, vp, u64, vp, C.POINTER(SeqView), C.POINTER(vp)]
     L.srgpu_graph_compact.argtypes = [vp]

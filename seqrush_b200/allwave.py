@@ -29,11 +29,25 @@ class AlignmentParams:  # allwave/src/types.rs:37-61 (defaults = seqrush -S 0,5,
     gap2_extend: Optional[int] = 1
     max_divergence: Optional[float] = None  # never read by the reference either
 
+    def mode(self) -> str:  # AlignmentMode::from_params, allwave/src/types.rs:101-111
+        if self.gap2_open is not None and self.gap2_extend is not None:
+            return "TwoPieceAffine"
+        if self.gap_open == self.gap_extend and self.gap_open == self.mismatch_penalty:
+            return "EditDistance"
+        return "SinglePieceAffine"
+
     def to_c(self) -> "_lib.Penalties":
-        if self.gap2_open is None or self.gap2_extend is None:
-            raise ValueError("only the two-piece affine mode (AlignmentMode::TwoPieceAffine) is implemented")
-        return _lib.Penalties(self.match_score, self.mismatch_penalty, self.gap_open, self.gap_extend,
-                              self.gap2_open, self.gap2_extend)
+        m = self.mode()
+        if m == "TwoPieceAffine":
+            return _lib.Penalties(self.match_score, self.mismatch_penalty, self.gap_open, self.gap_extend,
+                                  self.gap2_open, self.gap2_extend)
+        if m == "EditDistance":  # allwave/src/alignment.rs:205-213: affine with x, x, x
+            return _lib.Penalties(self.match_score, self.mismatch_penalty, self.mismatch_penalty, self.mismatch_penalty, -1, -1)
+        return _lib.Penalties(self.match_score, self.mismatch_penalty, self.gap_open, self.gap_extend, -1, -1)
+
+    @classmethod
+    def edit_distance(cls):  # allwave/src/types.rs:49-61
+        return cls(0, 1, 1, 1, None, None)
 
 
 def parse_scores(s: str) -> AlignmentParams:  # allwave/src/lib.rs:116-153
@@ -96,28 +110,30 @@ def alignment_to_paf(r: AlignmentResult, seqs: List[Sequence]) -> str:
 class AllPairIterator:
     """allwave/src/iterator.rs:12-253. ``with_options(sequences, params, exclude_self,
     use_mash_orientation, sparsification)``; iterating yields AlignmentResult in pair order
-    (the reference's rayon order is unspecified). Only SparsificationStrategy::None and an explicit
-    pair list are supported; mash orientation is not (the seqrush hot path passes false)."""
+    (the reference's rayon order is unspecified). ``sparsification`` is a SparsificationStrategy or the
+    string form of seqrush's -x flag (none | auto | random:F | connectivity:F | tree:kn[,kf[,rand[,k]]]); an
+    explicit ``pairs`` list overrides it. Mash orientation is not supported (the seqrush hot path passes false)."""
 
     def __init__(self, sequences: List[Sequence], params: AlignmentParams, exclude_self=True,
                  use_mash_orientation=False, sparsification=None, pairs=None, ctx=None):
         if use_mash_orientation:
             raise NotImplementedError("mash orientation is outside the seqrush hot path (seqrush.rs:733 passes false)")
-        if sparsification not in (None, "none", "None") and pairs is None:
-            raise NotImplementedError("pass an explicit pair list for sparsified runs")
+        from .sparsify import SparsificationStrategy, parse_sparsification, sparsified_pairs
+        if isinstance(sparsification, str):
+            sparsification = parse_sparsification(sparsification)
         self.sequences = sequences
         self.params = params
         self.ctx = ctx or default_context()
-        n = len(sequences)
-        if pairs is None:  # allwave/src/iterator.rs:37-46: i-major order, self pairs unless excluded
-            ii, jj = np.meshgrid(np.arange(n, dtype=np.uint32), np.arange(n, dtype=np.uint32), indexing="ij")
-            pr = np.stack([ii.ravel(), jj.ravel()], axis=1)
-            if exclude_self:
-                pr = pr[pr[:, 0] != pr[:, 1]]
-            self.pairs = np.ascontiguousarray(pr, dtype=np.uint32)
+        self._uploaded = False
+        if pairs is None:
+            # allwave/src/iterator.rs:37-77: i-major n^2 list (self pairs unless excluded), then the strategy
+            strat = sparsification or SparsificationStrategy.none()
+            if strat.kind == "tree":  # the sketches need the sequences on the device
+                self.ctx.set_sequences([s.seq for s in sequences])
+                self._uploaded = True
+            self.pairs = sparsified_pairs(sequences, strat, exclude_self, self.ctx, uploaded=self._uploaded)
         else:
             self.pairs = np.ascontiguousarray(np.asarray(pairs, dtype=np.uint32).reshape(-1, 2))
-        self._uploaded = False
 
     @classmethod
     def with_options(cls, sequences, params, exclude_self, use_mash_orientation, sparsification=None, **kw):

@@ -6,6 +6,7 @@
 #include "kernels.cuh"
 #include "graph.cuh"
 #include "graph_host.hpp"
+#include "sparsify.cuh"
 
 #include <algorithm>
 #include <functional>
@@ -351,19 +352,44 @@ static SeqTable seq_table(srgpu_ctx* c) {
   return t;
 }
 
+// allwave's three modes (allwave/src/alignment.rs:203-231, AlignmentMode::from_params allwave/src/types.rs:101-111) all
+// reach WFA2-lib as gap-affine or gap-affine-2p BiWFA:
+//   * two-piece affine (gap2 present)                         -> wavefront_penalties_set_affine2p
+//   * single-piece affine and "edit distance" (o = e = x)     -> wavefront_penalties_set_affine; run here as two EQUAL
+//     pieces: I2/D2 then duplicate I1/D1 cell for cell, every decision (limits, overlap order D before I before M,
+//     backtrace priority) picks an equivalent cell, score and CIGAR are those of the single-piece recurrence
+//   * match < 0: WFA2-lib's adjustment (Eizenga's formula, WFA/wavefront_penalties.c:113-134,157-175); match > 0 makes
+//     WFA2-lib print "Match score must be negative or zero" and exit(1) (:100-103,141-144) -> SRGPU_E_ARG here.
 static int check_penalties(const srgpu_penalties* p, Penalties* out) {
   if (!p) return SRGPU_E_ARG;
-  if (p->match_score != 0 || p->mismatch <= 0 || p->gap_open1 < 0 || p->gap_ext1 <= 0 || p->gap_open2 < 0 ||
-      p->gap_ext2 <= 0) {
-    g_err = "penalties: need match 0, mismatch > 0, gap_open >= 0, gap_ext > 0 (two-piece affine)";
+  if (p->match_score > 0) {
+    char b[128];
+    snprintf(b, sizeof b, "[WFA::Penalties] Match score must be negative or zero (M=%d)", p->match_score);
+    g_err = b;
     return SRGPU_E_ARG;
   }
-  out->x = p->mismatch;
-  out->o1 = p->gap_open1;
-  out->e1 = p->gap_ext1;
-  out->o2 = p->gap_open2;
-  out->e2 = p->gap_ext2;
-  out->scope = std::max(std::max(p->gap_open1 + p->gap_ext1, p->gap_open2 + p->gap_ext2), p->mismatch) + 1;
+  const bool two = p->gap_ext2 > 0;  // gap2 absent: gap_open2 / gap_ext2 <= 0 (None in allwave::AlignmentParams)
+  const int o2 = two ? p->gap_open2 : p->gap_open1, e2 = two ? p->gap_ext2 : p->gap_ext1;
+  if (p->mismatch <= 0 || p->gap_open1 < 0 || p->gap_ext1 <= 0 || o2 < 0 || e2 <= 0) {
+    g_err = "[WFA::Penalties] Penalties must be (X>0,O1>=0,E1>0,O2>=0,E2>0)";
+    return SRGPU_E_ARG;
+  }
+  const int m = p->match_score;
+  out->match = m;
+  if (m < 0) {
+    out->x = 2 * p->mismatch - 2 * m;
+    out->o1 = 2 * p->gap_open1;
+    out->e1 = 2 * p->gap_ext1 - m;
+    out->o2 = 2 * o2;
+    out->e2 = 2 * e2 - m;
+  } else {
+    out->x = p->mismatch;
+    out->o1 = p->gap_open1;
+    out->e1 = p->gap_ext1;
+    out->o2 = o2;
+    out->e2 = e2;
+  }
+  out->scope = std::max(std::max(out->o1 + out->e1, out->o2 + out->e2), out->x) + 1;
   if (out->scope + 1 > MAX_SCOPE) {
     g_err = "penalties too large: max_score_scope exceeds the ring depth (64)";
     return SRGPU_E_ARG;
@@ -437,11 +463,14 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
   // samples in profiles/r02d_*). SRGPU_STAGE_SEQS=0 / 1 forces either way.
   size_t smem_orient = (size_t)3 * c->max_pk_words * 4;
   if (smem_orient > (size_t)c->smem_budget) smem_orient = 0;
-  // launch shape: 128 threads x 4 CTAs/SM up to ~70 kb; longer sequences have wavefronts wide enough to
-  // keep 8 warps busy per pair and their staged sequences leave room for 2-3 CTAs only (measured on the
-  // 100 kb slice: 256x2 36.9 Mbp/s, 128x4 29.1)
+  // launch shape: 128 threads x 4 CTAs/SM. With the row staging in shared memory the sequences of a 100 kb pair no
+  // longer fit beside it at 4 CTAs/SM and are read from global memory, which still beats 256 x 2 with staged
+  // sequences there (400-pair slice of 100 x 100 kb: 854 ms against 967 ms, profiles/r02e_tune_c4s.log; in round 1,
+  // when every CTA had to stage its sequences, it was the other way round). Far longer sequences get 256 x 2: their
+  // wavefronts keep eight warps busy and half as many resident pairs halve the ring memory (174 MB per pair at
+  // 200 kb / 5 %).
   int threads = c->threads, ctas_per_sm = c->ctas_per_sm;
-  if (c->auto_shape && maxlen > 70000) {
+  if (c->auto_shape && maxlen > 150000) {
     threads = 256;
     ctas_per_sm = 2;
   }
@@ -543,11 +572,6 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
     int cur_grid = std::min<int>(grid, (int)cn);
     CK(cudaMemsetAsync(c->d_scalars.p, 0, 2 * sizeof(unsigned long long), c->stream));
     for (int attempt = 0;; ++attempt) {
-      if ((rc = c->d_ring.ensure((size_t)cur_grid * 2 * (pen.scope + 1) * 5 * curW))) return rc;
-      a.ring = c->d_ring.p;
-      a.ring_stride = (size_t)2 * (pen.scope + 1) * 5 * curW;
-      a.W = curW;
-      a.fixed_w = attempt > 0 ? 1 : 0;
       if (attempt == 0) {
         // strand choice of every pair of the chunk (its own launch: three staged sequences)
         AlignArgs ao = a;
@@ -559,7 +583,28 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
         CK(cudaGetLastError());
         CK(cudaEventRecord(c->ev[5], c->stream));
         c->stats.kernel_launches++;
+        if (c->ring_diagonals <= 0 && curW < fullW) {
+          // ring rows wide enough for the most divergent pair of the chunk (the kernel sizes each pair's rows as
+          // 8 x edit distance + 512 diagonals): one scalar read-back instead of a failed launch and a retry
+          unsigned int* d_maxed = (unsigned int*)(c->d_scalars.p + 2);
+          CK(cudaMemsetAsync(d_maxed, 0, sizeof(unsigned int), c->stream));
+          max_edit_distance_kernel<<<grid_for(cn, 256, c->n_sm), 256, 0, c->stream>>>(a.out, cn, d_maxed);
+          CK(cudaGetLastError());
+          unsigned int maxed = 0;
+          CK(cudaMemcpyAsync(&maxed, d_maxed, sizeof maxed, cudaMemcpyDeviceToHost, c->stream));
+          CK(cudaStreamSynchronize(c->stream));
+          c->stats.kernel_launches++;
+          const long long need = ((8ll * maxed + 512) + 63) & ~63ll;
+          if (need > curW) curW = (int)std::min<long long>(need, (fullW + 63) & ~63);
+          const size_t per = (size_t)2 * (pen.scope + 1) * 5 * curW * sizeof(int32_t);
+          cur_grid = (int)std::min<size_t>((size_t)cur_grid, std::max<size_t>(1, ((size_t)96 << 30) / per));
+        }
       }
+      if ((rc = c->d_ring.ensure((size_t)cur_grid * 2 * (pen.scope + 1) * 5 * curW))) return rc;
+      a.ring = c->d_ring.p;
+      a.ring_stride = (size_t)2 * (pen.scope + 1) * 5 * curW;
+      a.W = curW;
+      a.fixed_w = attempt > 0 ? 1 : 0;
       CK(cudaMemsetAsync(a.next_pair, 0, sizeof(unsigned int), c->stream));
       CK(cudaEventRecord(c->ev[1], c->stream));
       cudaError_t e = launch_align(a, threads, ctas_per_sm, cur_grid, smem, c->stream);
@@ -1438,3 +1483,120 @@ extern "C" int srgpu_graph_stats(srgpu_graph* gr, uint64_t* uncompacted_nodes, u
   return SRGPU_OK;
 }
 extern "C" void srgpu_graph_free(srgpu_graph* gr) { delete gr; }
+
+// ---------------------------------------------------------------------------
+// Pair-list sparsification (rows f2 / a5): MinHash sketches + Jaccard counts and the hashed pair filter on the
+// device (sparsify.cuh); reference allwave/src/mash.rs:30-165, allwave/src/knn_graph.rs:10-172,
+// allwave/src/iterator.rs:49-77,256-284.
+// ---------------------------------------------------------------------------
+extern "C" uint64_t srgpu_rust_hash_bytes(const uint8_t* data, uint64_t n) {  // DefaultHasher over a &[u8]
+  Sip13 h;
+  h.init();
+  h.word(n);
+  for (uint64_t i = 0; i < n; ++i) h.byte(data[i]);
+  return h.finish();
+}
+extern "C" uint64_t srgpu_rust_hash_str(const char* s) {  // DefaultHasher over a String / &str
+  Sip13 h;
+  h.init();
+  for (const char* p = s; *p; ++p) h.byte((unsigned char)*p);
+  h.byte(0xff);
+  return h.finish();
+}
+
+extern "C" int srgpu_mash_sketch_jaccard(srgpu_ctx* c, uint32_t k, uint32_t sketch_size, uint64_t* sketches_out,
+                                         uint32_t* counts_out, uint32_t* inter_out, uint32_t* uni_out) {
+  if (!c || k == 0 || sketch_size == 0 || sketch_size > (uint32_t)SKETCH_MAX) {
+    g_err = "mash sketch: k must be > 0 and 0 < sketch_size <= 4096";
+    return SRGPU_E_ARG;
+  }
+  std::lock_guard<std::mutex> lk(c->mu);
+  CK(cudaSetDevice(c->device));
+  const uint32_t n = c->n_seqs;
+  if (n == 0) return SRGPU_OK;
+  std::vector<unsigned long long> off(n + 1, 0);
+  for (uint32_t i = 0; i < n; ++i) off[i + 1] = off[i] + (c->h_len[i] >= k ? c->h_len[i] - k + 1 : 0);
+  DevBuf<unsigned long long> d_hash, d_off, d_sk;
+  DevBuf<unsigned int> d_cnt, d_skcnt, d_inter, d_uni;
+  int rc = 0;
+  auto cleanup = [&]() {
+    d_hash.release(); d_off.release(); d_sk.release(); d_cnt.release(); d_skcnt.release(); d_inter.release(); d_uni.release();
+  };
+  if ((rc = d_hash.ensure(off[n] + 1)) || (rc = d_off.ensure(n + 1)) || (rc = d_sk.ensure((size_t)n * sketch_size)) ||
+      (rc = d_cnt.ensure(n)) || (rc = d_skcnt.ensure(n)) || (rc = d_inter.ensure((size_t)n * n)) || (rc = d_uni.ensure((size_t)n * n))) {
+    cleanup();
+    return rc;
+  }
+  cudaError_t e = cudaMemcpyAsync(d_off.p, off.data(), (n + 1) * 8, cudaMemcpyHostToDevice, c->stream);
+  if (e == cudaSuccess) e = cudaMemsetAsync(d_cnt.p, 0, n * 4, c->stream);
+  if (e == cudaSuccess) e = cudaMemsetAsync(d_sk.p, 0, (size_t)n * sketch_size * 8, c->stream);
+  if (e == cudaSuccess) e = cudaMemsetAsync(d_inter.p, 0, (size_t)n * n * 4, c->stream);
+  if (e == cudaSuccess) e = cudaMemsetAsync(d_uni.p, 0, (size_t)n * n * 4, c->stream);
+  if (e == cudaSuccess) {
+    dim3 grid(std::max(1u, std::min(256u, (c->max_len + 255) / 256)), std::min(n, 65535u));
+    kmer_hash_kernel<<<grid, 256, 0, c->stream>>>(seq_table(c), k, d_off.p, d_hash.p, d_cnt.p);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) {
+    sketch_select_kernel<256><<<std::min<uint32_t>(n, (uint32_t)c->n_sm * 4), 256, 0, c->stream>>>(d_hash.p, d_off.p, d_cnt.p, n, sketch_size,
+                                                                                         d_sk.p, d_skcnt.p);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) {
+    jaccard_kernel<<<grid_for((uint64_t)n * n, 128, c->n_sm), 128, 0, c->stream>>>(d_sk.p, d_skcnt.p, n, sketch_size, d_inter.p, d_uni.p);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess && sketches_out) e = cudaMemcpyAsync(sketches_out, d_sk.p, (size_t)n * sketch_size * 8, cudaMemcpyDeviceToHost, c->stream);
+  if (e == cudaSuccess && counts_out) e = cudaMemcpyAsync(counts_out, d_skcnt.p, n * 4, cudaMemcpyDeviceToHost, c->stream);
+  if (e == cudaSuccess && inter_out) e = cudaMemcpyAsync(inter_out, d_inter.p, (size_t)n * n * 4, cudaMemcpyDeviceToHost, c->stream);
+  if (e == cudaSuccess && uni_out) e = cudaMemcpyAsync(uni_out, d_uni.p, (size_t)n * n * 4, cudaMemcpyDeviceToHost, c->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+  cleanup();
+  if (e != cudaSuccess) {
+    g_err = std::string("mash sketch: ") + cudaGetErrorString(e);
+    return SRGPU_E_CUDA;
+  }
+  c->stats.kernel_launches += 3;
+  return SRGPU_OK;
+}
+
+extern "C" int srgpu_pair_hash_filter(srgpu_ctx* c, const char* const* ids, uint32_t n, double fraction, int exclude_self,
+                                      uint8_t* keep_out, uint64_t* hashes_out) {
+  if (!c || !ids || !keep_out) return SRGPU_E_ARG;
+  std::lock_guard<std::mutex> lk(c->mu);
+  CK(cudaSetDevice(c->device));
+  if (n == 0) return SRGPU_OK;
+  std::vector<unsigned long long> off(n + 1, 0);
+  std::string cat;
+  for (uint32_t i = 0; i < n; ++i) {
+    if (!ids[i]) return SRGPU_E_ARG;
+    cat += ids[i];
+    off[i + 1] = cat.size();
+  }
+  DevBuf<uint8_t> d_ids, d_keep;
+  DevBuf<unsigned long long> d_off, d_h;
+  int rc = 0;
+  auto cleanup = [&]() { d_ids.release(); d_keep.release(); d_off.release(); d_h.release(); };
+  if ((rc = d_ids.ensure(cat.size() + 1)) || (rc = d_keep.ensure((size_t)n * n)) || (rc = d_off.ensure(n + 1)) ||
+      (hashes_out && (rc = d_h.ensure((size_t)n * n)))) {
+    cleanup();
+    return rc;
+  }
+  cudaError_t e = cudaMemcpyAsync(d_ids.p, cat.data(), cat.size(), cudaMemcpyHostToDevice, c->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(d_off.p, off.data(), (n + 1) * 8, cudaMemcpyHostToDevice, c->stream);
+  if (e == cudaSuccess) {
+    pair_hash_kernel<<<grid_for((uint64_t)n * n, 256, c->n_sm), 256, 0, c->stream>>>(d_ids.p, d_off.p, n, fraction, exclude_self, d_keep.p,
+                                                                               hashes_out ? d_h.p : nullptr);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaMemcpyAsync(keep_out, d_keep.p, (size_t)n * n, cudaMemcpyDeviceToHost, c->stream);
+  if (e == cudaSuccess && hashes_out) e = cudaMemcpyAsync(hashes_out, d_h.p, (size_t)n * n * 8, cudaMemcpyDeviceToHost, c->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+  cleanup();
+  if (e != cudaSuccess) {
+    g_err = std::string("pair hash filter: ") + cudaGetErrorString(e);
+    return SRGPU_E_CUDA;
+  }
+  c->stats.kernel_launches += 1;
+  return SRGPU_OK;
+}

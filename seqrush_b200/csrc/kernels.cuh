@@ -23,6 +23,7 @@ namespace srb {
 __device__ __forceinline__ uint32_t uf_find(uint32_t* __restrict__ parent, uint32_t x) {
   uint32_t p = parent[x];
   while (p != x) {
+    SR_ASSERT(p < x, "parent[x] <= x (links point to the smaller index)");
     const uint32_t gp = parent[p];
     if (gp != p) parent[x] = gp;
     x = p;
@@ -211,6 +212,13 @@ __global__ void __launch_bounds__(THREADS) orient_kernel(AlignArgs a) {
   }
 }
 
+__global__ void max_edit_distance_kernel(const PairOut* __restrict__ out, uint32_t n, unsigned int* result) {
+  unsigned int m = 0;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) m = max(m, out[i].edit_distance);
+  m = __reduce_max_sync(0xffffffffu, m);
+  if ((threadIdx.x & 31) == 0 && m) atomicMax(result, m);
+}
+
 template <int THREADS, int MIN_CTAS>
 __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
   // dynamic shared memory: [query strand chosen by orient_kernel | target] (smem_seq_words each; absent when the
@@ -325,6 +333,7 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
     if (st == ST_OK) {
       for (uint32_t i = threadIdx.x; i < r.n_runs; i += THREADS) {
         const uint32_t run = ro.runs[i];
+        SR_ASSERT(off + i < a.arena_cap, "CIGAR arena");
         a.arena[off + i] = run;
         const uint32_t op = run & 3u, len = run >> 2;
         if (op == OP_M) {

@@ -28,6 +28,23 @@
 #include <string.h>
 #endif
 
+// SRGPU_CHECKED build (development only, scripts/build_checked.sh): bounds assertions on every workspace this file
+// indexes -- ring rows, staging buffers, base-case store, run buffers -- that trap with a message. It stands in for
+// compute-sanitizer's memcheck, which is closed on the GPU pool this was developed on (profiles/r02h_*).
+#if defined(SRGPU_CHECKED) && defined(__CUDACC__) && !defined(WFA_HOST_EMULATION)
+#include <cstdio>
+#define SR_ASSERT(cond, what)                                                                                   \
+  do {                                                                                                          \
+    if (!(cond)) {                                                                                              \
+      printf("SRGPU_CHECKED: %s violated at %s:%d (CTA %d thread %d)\n", what, __FILE__, __LINE__, (int)blockIdx.x, \
+             (int)threadIdx.x);                                                                                 \
+      __trap();                                                                                                 \
+    }                                                                                                           \
+  } while (0)
+#else
+#define SR_ASSERT(cond, what) ((void)0)
+#endif
+
 namespace srb {
 
 static constexpr int32_t OFFSET_NULL = INT32_MIN / 2;  // WFA/wavefront_offset.h:44
@@ -54,8 +71,9 @@ enum : int {
 };
 
 struct Penalties {
-  int x, o1, e1, o2, e2;
+  int x, o1, e1, o2, e2;  // the penalties WFA2-lib computes with (after Eizenga's adjustment when match < 0)
   int scope;  // max_score_scope, WFA/wavefront_components.c:101-113
+  int match;  // the caller's match score (<= 0): only the reported score depends on it (WFA/wavefront_compute.c:108-120)
 };
 
 // absent wavefront (NULL pointer in the reference) == (1,-1) like its null wavefront
@@ -125,7 +143,11 @@ struct WfStore {
   WFA_FN int off_of(int s, int c) const { return (slot(s) * 5 + c) * W + (W >> 1); }  // modular rows only
   WFA_FN int32_t* row_of_slot(int sl, int c) const { return base + (uint32_t)((sl * 5 + c) * W + (W >> 1)); }
   WFA_FN int32_t* row(int s, int c) const {
-    if (modular) return row_of_slot(slot(s), c);
+    if (modular) {
+      SR_ASSERT(s > cur_s - scope && s <= cur_s && slot(s) >= 0 && slot(s) < scope, "ring slot of a live score");
+      return row_of_slot(slot(s), c);
+    }
+    SR_ASSERT(s >= 0 && s < cap && c >= 0 && c < 5, "base-case store row");
     return base + (size_t)c * (size_t)cap * (size_t)cap + (size_t)s * (size_t)s + s;
   }
   WFA_FN WfMeta get(int s, int c) const {
@@ -1125,6 +1147,9 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
 #pragma unroll
       for (int r = 0; r < 7; ++r) {
         const int off = sp[DS_O1 + r];
+        SR_ASSERT(!ok0 || (off + ks >= 0 && off + ks + 3 < 2 * df.st.scope * 5 * df.st.W), "row slice read inside the CTA's rings");
+        SR_ASSERT(!ok1 || (off + ks2 >= 0 && off + ks2 + 3 < 2 * df.st.scope * 5 * df.st.W), "row slice read inside the CTA's rings");
+        SR_ASSERT(((off + ks) & 3) == 0, "16-byte aligned row slice");
         if (ok0) cp_async16(wstage + r * STAGE_ROW + 4 * lane, ring + (off + ks));
         if (ok1) cp_async16(wstage + r * STAGE_ROW + 128 + 4 * lane, ring + (off + ks2));
       }
@@ -1266,6 +1291,9 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
     }
     // gap components of this score (rows of components that are not allocated this step are never
     // read: their meta says absent)
+    SR_ASSERT(!lane_act || (su[DS_WM] + k0 >= 0 && su[DS_WD2] + k0 + 3 < 2 * df.st.scope * 5 * df.st.W && su[DS_WM] + k0 + 3 < 2 * df.st.scope * 5 * df.st.W),
+              "row store inside the CTA's rings");
+    SR_ASSERT(!lane_act || (k0 >= -(df.st.W >> 1) && k0 + 3 < (df.st.W >> 1)), "diagonal inside the row");
     if (lane_act) {
       st4(ring + (su[DS_WI1] + k0), ins1[0], ins1[1], ins1[2], ins1[3]);
       st4(ring + (su[DS_WI2] + k0), ins2[0], ins2[1], ins2[2], ins2[3]);
@@ -1705,6 +1733,7 @@ WFA_FN bool runs_push(CtaShared* sh, const RunOut& ro, uint32_t op, uint32_t len
     return true;
   }
   if (sh->n_runs >= ro.cap) return false;
+  SR_ASSERT(sh->n_runs < ro.cap, "run buffer");
   ro.runs[sh->n_runs++] = make_run(op, len);
   return true;
 }
@@ -2007,7 +2036,11 @@ WFA_FN PairResult wf_align_pair(Ctx& cx, const SeqView& sv, int plen, int tlen, 
     cta_sync();
     const Breakpoint bp = sh->bp;
     const int bh = bp.offset_forward, bv = bp.offset_forward - bp.k_forward;
-    if (f.level == 0) level0_score = -bp.score;  // WFA/wavefront_bialign.c:1214-1219, match == 0
+    if (f.level == 0) {
+      // WFA/wavefront_bialign.c:1214-1219 -> wavefront_compute_classic_score (WFA/wavefront_compute.c:108-120):
+      // -score for match == 0, else WF_SCORE_TO_SW_SCORE = (swg_match * (plen + tlen) - score) / 2
+      level0_score = pen.match == 0 ? -bp.score : ((-pen.match) * (plen + tlen) - bp.score) / 2;
+    }
     cta_sync();
     if (cx.tid == 0) {
       if (sh->sp + 2 > STACK_MAX) {

@@ -104,6 +104,44 @@ class SeqRush:
         ii, jj = np.meshgrid(np.arange(n, dtype=np.uint32), np.arange(n, dtype=np.uint32), indexing="ij")
         return np.ascontiguousarray(np.stack([ii.ravel(), jj.ravel()], axis=1), dtype=np.uint32)
 
+    def pair_list(self, args: Args = None) -> np.ndarray:
+        """The pairs align_and_unite_with_allwave hands to AllPairIterator::with_options (:664-675, :728-735):
+        the n^2 i-major list including self pairs, thinned by -x/--sparsify (parse_sparsification, :356-431;
+        a string the reference cannot parse falls back to 'none' with a message, :668-674)."""
+        import sys
+        from .allwave import Sequence as AwSequence
+        from .sparsify import parse_sparsification, sparsified_pairs, SparsificationStrategy
+        args = args or Args()
+        spec = args.sparsification if args.sparsification not in (None, "None") else "none"
+        try:
+            strat = parse_sparsification(spec)
+        except ValueError as e:
+            print("Error parsing sparsification: %s. Using 'none'" % e, file=sys.stderr)
+            strat = SparsificationStrategy.none()
+        if strat.kind == "none":
+            return self.all_pairs()
+        aw = [AwSequence(s.id, s.data) for s in self.sequences]
+        return sparsified_pairs(aw, strat, False, self.ctx, uploaded=True)  # the context holds these sequences
+
+    def tree_pairs_separated(self, args: Args = None):
+        """extract_tree_pairs_separated for --iterative (:900-935): (tree pairs, random pairs)."""
+        from .allwave import Sequence as AwSequence
+        from .sparsify import parse_sparsification, extract_tree_pairs_separated
+        import sys
+        try:
+            strat = parse_sparsification((args or Args()).sparsification)
+        except ValueError as e:
+            print("Error parsing sparsification: %s. Using default tree:3,3,0.1,16" % e, file=sys.stderr)
+            strat = None
+        if strat is None or strat.kind != "tree":  # :925-935
+            if strat is not None:
+                print("Note: Iterative mode works best with tree sampling. Using default tree:3,3,0.1,16", file=sys.stderr)
+            kn, kf, rf, ks = 3, 3, 0.1, 16
+        else:
+            kn, kf, rf, ks = strat.k_nearest, strat.k_farthest, strat.random_fraction, strat.kmer_size or 16
+        aw = [AwSequence(s.id, s.data) for s in self.sequences]
+        return extract_tree_pairs_separated(aw, kn, kf, rf, ks, self.ctx, uploaded=True)
+
     def align_and_unite(self, args: Args = None, pairs=None, want_results=False):  # :460-508 -> :611-757
         args = args or Args()
         if args.paf:  # :463-466: a PAF file replaces the alignment phase
@@ -113,9 +151,7 @@ class SeqRush:
         if args.output_alignments:
             return self._align_write_paf_and_unite(args, pairs)
         if pairs is None:
-            if args.sparsification not in ("none", "None", None):
-                raise NotImplementedError("sparsified pair lists must be passed explicitly (pairs=...)")
-            pairs = self.all_pairs()
+            pairs = self.pair_list(args)
         pairs = np.ascontiguousarray(np.asarray(pairs, dtype=np.uint32).reshape(-1, 2))
         pen = parse_scores(args.scores).to_c()
         n = pairs.shape[0]
@@ -201,9 +237,10 @@ class SeqRush:
         (:976-991): (i,i), (i,j), (j,i), (j,j) in that order."""
         return [(i, i), (i, j), (j, i), (j, j)]
 
-    def align_and_unite_iterative(self, args: Args = None, tree_pairs=(), random_pairs=()):  # :868-1132
-        """--iterative with explicit pair lists (the reference derives them from MinHash sketches and
-        Rust's DefaultHasher, allwave/src/knn_graph.rs — not reproducible here). Phase 1
+    def align_and_unite_iterative(self, args: Args = None, tree_pairs=None, random_pairs=None):  # :868-1132
+        """--iterative. Without explicit lists the tree pairs and the random pairs come from
+        extract_tree_pairs_separated over the -x strategy (default tree:3,3,0.1,16; MinHash sketches and the
+        hashed pair filter on the device, seqrush_b200/sparsify.py), like the reference (:900-945). Phase 1
         runs every tree pair in one launch; phase 2 runs the random pairs CHECK_INTERVAL at a time and
         counts components on the device after each group, stopping after STABILITY_THRESHOLD unchanged
         counts in a row — the reference's check points, so the same prefix of random_pairs is processed
@@ -211,8 +248,10 @@ class SeqRush:
         args = args or Args()
         if args.output_alignments:
             raise NotImplementedError("--iterative with --output-alignments: write the PAF with align_and_unite")
-        tree_pairs = [(int(i), int(j)) for i, j in tree_pairs]
-        random_pairs = [(int(i), int(j)) for i, j in random_pairs]
+        if tree_pairs is None and random_pairs is None:
+            tree_pairs, random_pairs = self.tree_pairs_separated(args)
+        tree_pairs = [(int(i), int(j)) for i, j in (tree_pairs or ())]
+        random_pairs = [(int(i), int(j)) for i, j in (random_pairs or ())]
         sub = Args(scores=args.scores, min_match_length=args.min_match_length)
         if tree_pairs:
             self.align_and_unite(sub, pairs=[q for p in tree_pairs for q in self._expand_pair(*p)])

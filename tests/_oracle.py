@@ -54,6 +54,7 @@ def lib():
     L.orc_align_pair.argtypes = [vp, vp, i32, vp, i32, C.POINTER(i32), C.c_char_p] + [C.POINTER(i32)] * 5
     L.orc_wfa_only.argtypes = [vp, vp, i32, vp, i32, vp, i32, C.c_char_p, C.POINTER(i32), C.POINTER(i32)]
     L.orc_edlib.argtypes = [vp, vp, i32, vp, i32]
+    L.orc_wfa_mode.argtypes = [vp, vp, i32, vp, i32, vp, i32, C.c_char_p, C.POINTER(i32), C.POINTER(i32)]
     L.orc_cigar_bytes_to_string.argtypes = [C.c_char_p, i32, C.c_char_p, i32]
     L.orc_uf_new.restype = vp
     L.orc_uf_new.argtypes = [u64]
@@ -75,6 +76,20 @@ def lib():
     L.orc_process_alignment.argtypes = [vp, C.c_char_p, vp, u64, u64, vp, u64, u64, u64, i32, u64, u64]
     L.orc_run_pairs.argtypes = [vp, vp, vp, vp, C.c_uint32, vp, u64, C.POINTER(i32), u64, i32, vp, C.POINTER(RunStats)]
     L.orc_swg2p_penalty.argtypes = [vp, i32, vp, i32, C.POINTER(i32)]
+    L.orc_siphash.restype = u64
+    L.orc_siphash.argtypes = [C.c_char_p, u64, u64, u64, i32, i32]
+    L.orc_rust_hash_bytes.restype = u64
+    L.orc_rust_hash_bytes.argtypes = [C.c_char_p, u64]
+    L.orc_rust_hash_str.restype = u64
+    L.orc_rust_hash_str.argtypes = [C.c_char_p]
+    L.orc_sketch.restype = u64
+    L.orc_sketch.argtypes = [vp, u64, u64, u64, vp]
+    L.orc_tree_pairs.restype = u64
+    L.orc_tree_pairs.argtypes = [vp, vp, vp, C.c_uint32, u64, u64, C.c_double, u64, i32, vp, u64, C.POINTER(u64), vp]
+    L.orc_random_pairs.restype = u64
+    L.orc_random_pairs.argtypes = [vp, C.c_uint32, i32, C.c_double, vp, u64]
+    L.orc_connectivity_probability.restype = C.c_double
+    L.orc_connectivity_probability.argtypes = [u64, C.c_double]
     L.orc_build_gfa.restype = vp
     L.orc_build_gfa.argtypes = [vp, vp, vp, C.c_uint32, vp, i32, vp, C.POINTER(u64)]
     L.orc_free.argtypes = [vp]
@@ -112,6 +127,17 @@ class Oracle:
         n, score = C.c_int(), C.c_int()
         st = lib().orc_wfa_only(self.h, p.ctypes.data, p.size, t.ctypes.data, t.size, (C.c_int * 5)(*pen), memory_mode,
                                 buf, C.byref(n), C.byref(score))
+        return st, score.value, buf.raw[:n.value]
+
+    def wfa_mode(self, p, t, pen6, two_piece=True):
+        """BiWFA under any of allwave's modes: pen6 = (match <= 0, x, o1, e1, o2, e2) -> (status, score, cigar)."""
+        p, t = self._arr(p), self._arr(t)
+        buf = C.create_string_buffer(p.size + t.size + 16)
+        n, score = C.c_int(), C.c_int()
+        st = lib().orc_wfa_mode(self.h, p.ctypes.data, p.size, t.ctypes.data, t.size, (C.c_int * 6)(*pen6),
+                                int(bool(two_piece)), buf, C.byref(n), C.byref(score))
+        if st == -100:
+            raise RuntimeError("oracle/_ref predates ref_wfa_new_mode: rebuild it with `make -C oracle all`")
         return st, score.value, buf.raw[:n.value]
 
     def edlib(self, q, t):
@@ -182,6 +208,40 @@ class OracleUF:
         a, b = Oracle._arr(d1), Oracle._arr(d2)
         return lib().orc_process_alignment(self.h, cigar.encode(), a.ctypes.data, a.size, o1, b.ctypes.data, b.size,
                                            o2, min_match_len, int(bool(query_is_rc)), qstart, tstart)
+
+
+def siphash(data: bytes, k0=0, k1=0, c=1, d=3):
+    return lib().orc_siphash(data, len(data), k0, k1, c, d)
+
+
+def sketch(seq, k, sketch_size=1000):
+    a = Oracle._arr(seq)
+    out = np.zeros(sketch_size, dtype=np.uint64)
+    n = lib().orc_sketch(a.ctypes.data, a.size, k, sketch_size, out.ctypes.data)
+    return out[:n]
+
+
+def tree_pairs(seqs, ids, k_nearest, k_farthest, random_fraction, kmer_size, separated=False):
+    """extract_tree_pairs[_separated] restated: (pairs, n_tree, distance matrix)."""
+    arrs = [Oracle._arr(s) for s in seqs]
+    n = len(arrs)
+    ptrs = (C.c_void_p * n)(*[a.ctypes.data for a in arrs])
+    lens = np.array([a.size for a in arrs], dtype=np.uint64)
+    names = (C.c_char_p * n)(*[i.encode() for i in ids])
+    out = np.zeros((n * n + 1, 2), dtype=np.uint32)
+    nt = C.c_uint64()
+    dist = np.zeros((n, n), dtype=np.float64)
+    m = lib().orc_tree_pairs(ptrs, lens.ctypes.data, names, n, k_nearest, k_farthest, random_fraction, kmer_size,
+                             int(bool(separated)), out.ctypes.data, out.shape[0], C.byref(nt), dist.ctypes.data)
+    return out[:m].copy(), nt.value, dist
+
+
+def random_pairs(ids, exclude_self, keep_fraction):
+    n = len(ids)
+    names = (C.c_char_p * n)(*[i.encode() for i in ids])
+    out = np.zeros((n * n + 1, 2), dtype=np.uint32)
+    m = lib().orc_random_pairs(names, n, int(bool(exclude_self)), keep_fraction, out.ctypes.data, out.shape[0])
+    return out[:m].copy()
 
 
 def build_gfa(uf, seqs, ids, no_compact=False):

@@ -495,3 +495,61 @@ def test_graph_build_and_gfa(s, oracle, c1_golden):
     out.close()
     g.close()
     ctx.close()
+
+
+def test_alignment_modes_and_aligner_trait(s, oracle):
+    """allwave's three modes (allwave/src/alignment.rs:203-231) and negative match scores through the C ABI against
+    WFA2-lib itself (oracle/_ref, gap-affine / gap-affine-2p BiWFA with the same penalties): raw score and CIGAR;
+    then the Aligner trait surface (src/aligner.rs:12-33,64-96; src/aligner/allwave_impl.rs:95-148)."""
+    from seqrush_b200 import synth
+    rng = np.random.default_rng(77)
+    acgt = np.frombuffer(b"ACGT", dtype=np.uint8)
+    seqs = []
+    for L, d in ((90, 0.05), (700, 0.03), (3000, 0.02), (9000, 0.04), (2500, 0.10)):
+        anc = acgt[rng.integers(0, 4, size=L)]
+        seqs += [synth.mutate(rng, anc, d).tobytes(), synth.mutate(rng, anc, d).tobytes()]
+    anc = acgt[rng.integers(0, 4, size=4000)]
+    a = synth.mutate(rng, anc, 0.01)
+    seqs += [a.tobytes(), np.concatenate([a[:1500], a[1900:]]).tobytes()]  # a 400-base gap
+    pairs = [(i, i + 1) for i in range(0, len(seqs), 2)] + [(i + 1, i) for i in range(0, len(seqs), 2)]
+    cases = [
+        (s.AlignmentParams(0, 5, 8, 2, None, None), (0, 5, 8, 2, 0, 0), False),     # single-piece affine
+        (s.AlignmentParams(0, 4, 6, 2, None, None), (0, 4, 6, 2, 0, 0), False),
+        (s.AlignmentParams.edit_distance(), (0, 1, 1, 1, 0, 0), False),              # "edit distance" = affine 1,1,1
+        (s.AlignmentParams(0, 3, 3, 3, None, None), (0, 3, 3, 3, 0, 0), False),
+        (s.AlignmentParams(-1, 4, 6, 2, 24, 1), (-1, 4, 6, 2, 24, 1), True),         # match < 0: Eizenga's adjustment
+        (s.AlignmentParams(-2, 4, 4, 2, 24, 1), (-2, 4, 4, 2, 24, 1), True),         # the trait's defaults with the sign WFA2-lib takes
+        (s.AlignmentParams(-1, 3, 5, 1, None, None), (-1, 3, 5, 1, 0, 0), False),
+    ]
+    for params, pen6, two in cases:
+        res = _align(s, seqs, pairs, params)
+        for r in res:
+            q = seqs[r.query_idx]
+            if r.is_reverse:
+                q = s.reverse_complement(q)
+            st, score, cig = oracle.wfa_mode(q, seqs[r.target_idx], pen6, two)
+            assert st == 0 and r.cigar_bytes == cig and r.score == score, (pen6, r.query_idx, r.target_idx, r.score, score)
+    with pytest.raises(s.SrgpuError, match="Match score must be negative or zero"):
+        _align(s, seqs[:2], [(0, 1)], s.AlignmentParams(2, 4, 4, 2, 24, 1))
+    # the trait
+    ctx = s.Context(0)
+    al = s.AllwaveAligner.with_params(1, False, s.AlignmentParams(), ctx=ctx)
+    recs = al.align_sequences([s.AlignmentSequence("s%d" % i, b) for i, b in enumerate(seqs[:6])])
+    assert len(recs) == 36 and isinstance(s.create_aligner("AllWave", 1, False, None, ctx=ctx), s.AllwaveAligner)
+    k = 0
+    for i in range(6):
+        for j in range(6):
+            o = oracle.align_pair(seqs[i], seqs[j])
+            r = recs[k]
+            k += 1
+            assert (r.query_name, r.target_name, r.query_len, r.target_len) == ("s%d" % i, "s%d" % j, len(seqs[i]), len(seqs[j]))
+            assert r.strand == ("-" if o["is_reverse"] else "+") and r.cigar == s.cigar_bytes_to_string(o["cigar"])
+            assert (r.query_start, r.query_end, r.target_start, r.target_end) == (0, len(seqs[i]), 0, len(seqs[j]))
+    with pytest.raises(s.SrgpuError, match="Match score"):
+        s.create_aligner("allwave", ctx=ctx).align_sequences([s.AlignmentSequence("a", seqs[0]), s.AlignmentSequence("b", seqs[1])])
+    with pytest.raises(RuntimeError):
+        s.create_aligner("sweepga")
+    with pytest.raises(ValueError):
+        s.create_aligner("minimap2")
+    assert s.AllwaveAligner.get_prioritized_pairs([s.AlignmentSequence("a", seqs[0]), s.AlignmentSequence("b", seqs[1])], "none", ctx=ctx) == [(0, 0), (0, 1), (1, 0), (1, 1)]
+    ctx.close()

@@ -30,8 +30,13 @@ def test_allwave_helpers():
     assert s.parse_scores("0,5,8,2").gap2_open is None
     with pytest.raises(ValueError):
         s.parse_scores("1,2,3")
-    with pytest.raises(ValueError):
-        s.parse_scores("0,5,8,2").to_c()
+    # AlignmentMode::from_params (allwave/src/types.rs:101-111) and what reaches the C ABI for each mode
+    assert s.parse_scores("0,5,8,2,24,1").mode() == "TwoPieceAffine" and s.parse_scores("0,5,8,2").mode() == "SinglePieceAffine"
+    assert s.AlignmentParams.edit_distance().mode() == "EditDistance"
+    c = s.parse_scores("0,5,8,2").to_c()
+    assert (c.mismatch, c.gap_open1, c.gap_ext1, c.gap_open2, c.gap_ext2) == (5, 8, 2, -1, -1)
+    c = s.AlignmentParams(0, 3, 3, 3, None, None).to_c()  # "edit distance" = affine x, x, x (allwave/src/alignment.rs:205-213)
+    assert (c.mismatch, c.gap_open1, c.gap_ext1, c.gap_ext2) == (3, 3, 3, -1)
 
 
 def test_paf_line():
