@@ -200,6 +200,16 @@ int srgpu_uf_unite_fr_all(srgpu_uf* uf, uint64_t total_length);
 int srgpu_uf_roots(srgpu_uf* uf, uint64_t first, uint64_t n, uint64_t* out);
 /* count_components (src/seqrush.rs:341-353): distinct representatives over forward Pos. */
 int srgpu_uf_count_components(srgpu_uf* uf, uint64_t total_length, uint64_t* count);
+/* count_components WITHOUT any allocation. This entry point has no counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it). Same result as srgpu_uf_count_components; the kernel's scratch (a 64-bit
+ * counter and a bitmap with one bit per Pos) is a file-scope __device__ array of 4 MiB + 256 B that every GPU loading
+ * the library holds until exit. Limit: union-finds of at most srgpu_uf_count_components_static_max_capacity() =
+ * 33 554 432 Pos (16 777 215 bases); larger ones are refused with SRGPU_E_ARG. It calls no cudaMalloc / cudaFree or
+ * allocating library routine. Every call shares the one array (it is cleared at the start of each call): calls that
+ * overlap on the same GPU race -- serialise them. */
+int srgpu_uf_count_components_static(srgpu_uf* uf, uint64_t total_length, uint64_t* count);
+uint64_t srgpu_uf_count_components_static_max_capacity(void);
 /* 64-bit order-independent checksum of the canonical partition (sum over p of mix(p, find(p))). */
 int srgpu_uf_checksum(srgpu_uf* uf, uint64_t* checksum);
 /* Multi-GPU merge (one process per GPU): device pointer + element count of the uint32 parent

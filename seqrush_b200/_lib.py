@@ -26,6 +26,7 @@ EXPORTS = [
     "srgpu_uf_unite_matching_region", "srgpu_uf_unite_matching_region_seq2_rc", "srgpu_uf_unite_regions",
     "srgpu_uf_unite_fr_all", "srgpu_uf_roots", "srgpu_uf_count_components", "srgpu_uf_checksum",
     "srgpu_uf_device_ptr", "srgpu_uf_compress", "srgpu_uf_merge_roots",
+    "srgpu_uf_count_components_static", "srgpu_uf_count_components_static_max_capacity",
     "srgpu_rust_hash_bytes", "srgpu_rust_hash_str", "srgpu_mash_sketch_jaccard", "srgpu_pair_hash_filter",
     "srgpu_graph_build", "srgpu_graph_from_parts", "srgpu_graph_compact", "srgpu_graph_node_count", "srgpu_graph_edge_count",
     "srgpu_graph_path_count", "srgpu_graph_path_length", "srgpu_graph_path_steps", "srgpu_graph_node_sequence",
@@ -144,6 +145,9 @@ def lib():
     L.srgpu_uf_roots.argtypes = [vp, u64, u64, vp]
     L.srgpu_uf_count_components.argtypes = [vp, u64, C.POINTER(u64)]
     L.srgpu_uf_checksum.argtypes = [vp, C.POINTER(u64)]
+    L.srgpu_uf_count_components_static.argtypes = [vp, u64, C.POINTER(u64)]
+    L.srgpu_uf_count_components_static_max_capacity.argtypes = []
+    L.srgpu_uf_count_components_static_max_capacity.restype = u64
     L.srgpu_uf_device_ptr.argtypes = [vp]
     L.srgpu_uf_device_ptr.restype = vp
     L.srgpu_uf_compress.argtypes = [vp]

@@ -1600,3 +1600,71 @@ extern "C" int srgpu_pair_hash_filter(srgpu_ctx* c, const char* const* ids, uint
   c->stats.kernel_launches += 1;
   return SRGPU_OK;
 }
+
+// ---------------------------------------------------------------------------
+// Allocation-free variant of srgpu_uf_count_components. No counterpart in the reference: added
+// for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses
+// that forbid it). The scratch of uf_count_kernel -- one 64-bit counter and a bitmap with one bit per Pos -- lives
+// in a file-scope __device__ array of fixed size: every GPU that loads the library holds these 4 MiB + 256 B until
+// the process exits. All calls share the array and it keeps the last call's contents, so each call clears the part
+// it uses; two calls that overlap on the GPU (different streams / contexts of one device) race on it.
+// ---------------------------------------------------------------------------
+static constexpr uint64_t STATIC_BITMAP_WORDS = 1ull << 20;                 // 4 MiB: one bit per Pos
+static constexpr uint64_t STATIC_MAX_CAPACITY = STATIC_BITMAP_WORDS * 32;   // 33 554 432 Pos = 16 777 215 bases
+static __device__ __align__(256) uint32_t g_count_scratch[64 + STATIC_BITMAP_WORDS];  // [0..63]: counter (256 B), then the bitmap
+
+// In host code `g_count_scratch` is a host-side stand-in, not a device address: the device address is looked up once
+// per device, with that device current, and cached.
+static std::mutex g_scratch_mu;
+static uint32_t* g_scratch_addr[64] = {nullptr};
+static int count_scratch_address(int device, uint32_t** out) {
+  if (device < 0 || device >= 64) {
+    g_err = "device index out of range for the static scratch table";
+    return SRGPU_E_ARG;
+  }
+  std::lock_guard<std::mutex> lk(g_scratch_mu);
+  if (!g_scratch_addr[device]) {
+    void* p = nullptr;
+    CK(cudaSetDevice(device));
+    CK(cudaGetSymbolAddress(&p, g_count_scratch));
+    g_scratch_addr[device] = (uint32_t*)p;
+  }
+  *out = g_scratch_addr[device];
+  return 0;
+}
+
+extern "C" uint64_t srgpu_uf_count_components_static_max_capacity(void) { return STATIC_MAX_CAPACITY; }
+
+extern "C" int srgpu_uf_count_components_static(srgpu_uf* u, uint64_t total_length, uint64_t* count) {
+  if (!u || !count) return SRGPU_E_ARG;
+  UF_ALIVE(u);
+  srgpu_ctx* c = u->ctx;
+  std::lock_guard<std::mutex> lk(c->mu);
+  CK(cudaSetDevice(c->device));
+  if (2 * total_length > u->capacity) {
+    g_err = "Pos out of range";
+    return SRGPU_E_RANGE;
+  }
+  if (u->capacity > STATIC_MAX_CAPACITY) {
+    char b[200];
+    snprintf(b, sizeof b, "union-find of %llu Pos exceeds the static scratch of srgpu_uf_count_components_static "
+             "(%llu Pos = 4 MiB bitmap); use srgpu_uf_count_components", (unsigned long long)u->capacity,
+             (unsigned long long)STATIC_MAX_CAPACITY);
+    g_err = b;
+    return SRGPU_E_ARG;
+  }
+  uint32_t* scratch = nullptr;
+  int rc;
+  if ((rc = count_scratch_address(c->device, &scratch))) return rc;
+  unsigned long long* d_count = (unsigned long long*)scratch;
+  uint32_t* d_bitmap = scratch + 64;
+  const size_t words = (u->capacity + 31) / 32;
+  CK(cudaMemsetAsync(scratch, 0, (64 + words) * 4, c->stream));  // the array keeps the last call's contents
+  if (total_length) {
+    uf_count_kernel<<<grid_for(total_length, 256, c->n_sm), 256, 0, c->stream>>>(u->parent.p, total_length, d_bitmap, d_count);
+    CK(cudaGetLastError());
+  }
+  CK(cudaMemcpyAsync(count, d_count, 8, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  return SRGPU_OK;
+}
