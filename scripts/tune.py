@@ -31,6 +31,6 @@ for cfg in configs:
         dt = time.time() - t0
     ck = sr.union_find.checksum()
     ref_ck = ref_ck or ck
-    print("cfg %s: %.3f s  align_ms %.1f union_ms %.2f  launches %d retries %d  %.1f Mbp/s  cells/s %.3g  checksum %s"
-          % (cfg, dt, st["align_ms"], st["union_ms"], st["kernel_launches"], st["retries"],
+    print("cfg %s: %.3f s  align_ms %.1f orient_ms %.1f union_ms %.2f  launches %d retries %d  %.1f Mbp/s  cells/s %.3g  checksum %s"
+          % (cfg, dt, st["align_ms"], st["orient_ms"], st["union_ms"], st["kernel_launches"], st["retries"],
              st["aligned_bp"] / 1e6 / dt, st["wf_cells"] / (st["align_ms"] / 1e3), "same" if ck == ref_ck else "DIFF"), flush=True)

@@ -88,6 +88,7 @@ struct srgpu_ctx {
   int lbits = 3;              // log2(bits per packed symbol): 1, 2 or 3
   uint32_t max_pk_words = 0;  // packed words of the longest sequence incl. guards
   int smem_budget = 96 * 1024;  // dynamic shared memory a kernel may use for staged sequences
+  int orient_ctas_per_sm = 6;   // SRGPU_ORIENT_CTAS (tuning; c2: 4 -> 36 ms, 6 -> 27 ms, 8 -> 27 ms, profiles/r02o_*)
   int stage_seqs = -1;          // align_kernel: stage the two sequences (-1: when the CTAs per SM are kept; SRGPU_STAGE_SEQS=0/1)
   DevBuf<uint32_t> d_len;
   std::vector<uint32_t> h_len;
@@ -160,6 +161,7 @@ extern "C" int srgpu_ctx_create(int device, void* stream, srgpu_ctx** out) {
   }
   for (int i = 0; i < 6; ++i) CK(cudaEventCreate(&c->ev[i]));
   if (const char* e = getenv("SRGPU_SMEM_BUDGET")) c->smem_budget = atoi(e);  // tuning: 0 = never stage sequences
+  if (const char* e = getenv("SRGPU_ORIENT_CTAS")) c->orient_ctas_per_sm = std::max(1, atoi(e));
   if (const char* e = getenv("SRGPU_STAGE_SEQS")) c->stage_seqs = atoi(e) != 0 ? 1 : 0;
   *out = c;
   return SRGPU_OK;
@@ -503,7 +505,21 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
   if ((rc = c->d_scalars.ensure(16))) return rc;
   if ((rc = c->d_full.ensure((size_t)grid * 5 * cap * cap))) return rc;
   if ((rc = c->d_full_meta.ensure((size_t)grid * cap * 5))) return rc;
-  if ((rc = c->d_orient.ensure((size_t)grid * 4 * orient_row))) return rc;
+  // the strand-choice kernel needs 32 registers and is bound by the latency of its global-memory rows (ncu: long
+  // scoreboard 3.8 cycles per issue at 17 % warps active when it ran on the align kernel's grid, profiles/r02n_*): it
+  // gets its own grid, as many CTAs per SM as its staged sequences allow (at most 8)
+  int orient_grid = grid;
+  {
+    int nb = 0;
+    cudaFuncSetAttribute(orient_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_orient);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, orient_kernel<128>, 128, smem_orient) == cudaSuccess && nb > 0)
+      orient_grid = c->n_sm * std::min(nb, c->orient_ctas_per_sm);
+    // keep the four edit-distance rows of every CTA within ~16 GB
+    const size_t per = (size_t)4 * orient_row * sizeof(int32_t);
+    orient_grid = (int)std::min<size_t>((size_t)orient_grid, std::max<size_t>(1, ((size_t)16 << 30) / per));
+    if ((uint64_t)orient_grid > n_pairs) orient_grid = (int)n_pairs;
+  }
+  if ((rc = c->d_orient.ensure((size_t)orient_grid * 4 * orient_row))) return rc;
   if ((rc = c->d_runs_tmp.ensure((size_t)grid * runs_cap))) return rc;
   if ((rc = c->d_bt_tmp.ensure((size_t)grid * runs_cap))) return rc;
   // arena: run-length CIGAR elements of one chunk
@@ -579,7 +595,7 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
         CK(cudaMemsetAsync(a.next_pair, 0, sizeof(unsigned int), c->stream));
         CK(cudaEventRecord(c->ev[4], c->stream));
         CK(cudaFuncSetAttribute(orient_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_orient));
-        orient_kernel<128><<<cur_grid, 128, smem_orient, c->stream>>>(ao);
+        orient_kernel<128><<<std::min<int>(orient_grid, (int)cn), 128, smem_orient, c->stream>>>(ao);
         CK(cudaGetLastError());
         CK(cudaEventRecord(c->ev[5], c->stream));
         c->stats.kernel_launches++;

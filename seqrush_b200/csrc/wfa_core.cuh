@@ -838,6 +838,10 @@ WFA_FN void cp_async16(int32_t* dst_smem, const int32_t* src_gmem) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src_gmem)
                : "memory");
 }
+WFA_FN void cp_async4(int32_t* dst_smem, const int32_t* src_gmem) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src_gmem)
+               : "memory");
+}
 WFA_FN void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 WFA_FN void cp_async_wait() {
@@ -1140,18 +1144,26 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
   auto prefetch = [&](int pdir, int pkb) {
     if (pdir >= 0) {
       const volatile int* sp = cx.sh->ds[pdir];
-      const int phi = sp[DS_HI] + 4;
-      const int ks = pkb - 4 + 4 * lane;   // segment `lane`
-      const int ks2 = ks + 128;            // segments 32, 33 (lanes 0 and 1)
-      const bool ok0 = ks <= phi, ok1 = lane < 2 && ks2 <= phi;
+      const int phi = sp[DS_HI];
+      const int ks = pkb + 4 * lane;  // this lane's own four diagonals
+      const bool ok0 = ks <= phi + 4;
 #pragma unroll
       for (int r = 0; r < 7; ++r) {
         const int off = sp[DS_O1 + r];
         SR_ASSERT(!ok0 || (off + ks >= 0 && off + ks + 3 < 2 * df.st.scope * 5 * df.st.W), "row slice read inside the CTA's rings");
-        SR_ASSERT(!ok1 || (off + ks2 >= 0 && off + ks2 + 3 < 2 * df.st.scope * 5 * df.st.W), "row slice read inside the CTA's rings");
         SR_ASSERT(((off + ks) & 3) == 0, "16-byte aligned row slice");
-        if (ok0) cp_async16(wstage + r * STAGE_ROW + 4 * lane, ring + (off + ks));
-        if (ok1) cp_async16(wstage + r * STAGE_ROW + 128 + 4 * lane, ring + (off + ks2));
+        if (ok0) cp_async16(wstage + r * STAGE_ROW + 4 + 4 * lane, ring + (off + ks));
+      }
+      // the eight neighbours outside the chunk in ONE 4-byte copy instruction: lanes 0..3 fetch diagonal kb-1 of
+      // o1, o2, i1, i2 (the k-1 sources of the chunk's first cell), lanes 4..7 diagonal kb+128 of o1, o2, d1, d2
+      // (the k+1 sources of its last cell)
+      if (lane < 8) {
+        const int r = lane < 4 ? lane : (lane < 6 ? lane - 4 : lane - 2);  // DS_O1.. order: o1 o2 i1 i2 d1 d2 mis
+        const int k = lane < 4 ? pkb - 1 : pkb + 128;
+        if (lane < 4 || k <= phi + 7) {
+          SR_ASSERT(sp[DS_O1 + r] + k >= 0 && sp[DS_O1 + r] + k < 2 * df.st.scope * 5 * df.st.W, "edge neighbour inside the CTA's rings");
+          cp_async4(wstage + r * STAGE_ROW + (lane < 4 ? 3 : 132), ring + (sp[DS_O1 + r] + k));
+        }
       }
     }
     cp_async_commit();
