@@ -100,12 +100,23 @@ struct srgpu_ctx {
   DevBuf<uint2> d_pairs;
   DevBuf<PairOut> d_out;
   DevBuf<uint32_t> d_arena, d_todo;
-  DevBuf<unsigned long long> d_scalars;  // [0] arena_head, [1] next_pair(uint) , [4..8] counters
+  DevBuf<unsigned long long> d_scalars;  // [0] arena_head, [1] next_pair(uint), [2] max edit distance, [3] task_count, [4] next_task
+  // split mode: tasks (sub-problems) and the workspaces of the one-warp kernel that solves them
+  int split_T = 1000;  // sub-problems whose score_remaining is at most this go to subalign_kernel (0: monolithic); SRGPU_SPLIT_T.
+                       // 1500-pair slices: c2 840 ms monolithic, 728 / 740 / 766 / 831 at T = 500 / 1000 / 1900 / 3900; 100 kb 2837 -> 2756 / 2737 / 2717
+                       // (profiles/r02t_*, r02u_*, r02v_*)
+  DevBuf<Frame> d_tasks;
+  DevBuf<uint32_t> d_task_pair;
+  DevBuf<TaskOut> d_task_out;
+  DevBuf<SplitRec> d_split;
+  DevBuf<int32_t> d_ring2, d_full2;
+  DevBuf<WfMeta> d_full_meta2;
+  DevBuf<uint32_t> d_runs_tmp2, d_bt_tmp2;
   DevBuf<unsigned long long> d_byteoff;
   DevBuf<uint8_t> d_bytes;
   DevBuf<PafRecordDev> d_paf_recs;
   DevBuf<unsigned long long> d_paf_runs;
-  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev[10] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   srgpu_stats stats{};
   std::vector<srgpu_uf*> ufs;  // union-finds living on this context (orphaned when it is destroyed)
 };
@@ -159,8 +170,9 @@ extern "C" int srgpu_ctx_create(int device, void* stream, srgpu_ctx** out) {
     CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     c->own_stream = true;
   }
-  for (int i = 0; i < 6; ++i) CK(cudaEventCreate(&c->ev[i]));
+  for (int i = 0; i < 10; ++i) CK(cudaEventCreate(&c->ev[i]));
   if (const char* e = getenv("SRGPU_SMEM_BUDGET")) c->smem_budget = atoi(e);  // tuning: 0 = never stage sequences
+  if (const char* e = getenv("SRGPU_SPLIT_T")) c->split_T = atoi(e);
   if (const char* e = getenv("SRGPU_ORIENT_CTAS")) c->orient_ctas_per_sm = std::max(1, atoi(e));
   if (const char* e = getenv("SRGPU_STAGE_SEQS")) c->stage_seqs = atoi(e) != 0 ? 1 : 0;
   *out = c;
@@ -180,7 +192,9 @@ extern "C" void srgpu_ctx_destroy(srgpu_ctx* c) {
   c->d_len.release(); c->d_ring.release(); c->d_full.release(); c->d_orient.release(); c->d_full_meta.release();
   c->d_runs_tmp.release(); c->d_bt_tmp.release(); c->d_pairs.release(); c->d_out.release(); c->d_arena.release();
   c->d_todo.release(); c->d_scalars.release(); c->d_byteoff.release(); c->d_bytes.release(); c->d_paf_recs.release(); c->d_paf_runs.release();
-  for (int i = 0; i < 6; ++i) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+  c->d_tasks.release(); c->d_task_pair.release(); c->d_task_out.release(); c->d_split.release(); c->d_ring2.release();
+  c->d_full2.release(); c->d_full_meta2.release(); c->d_runs_tmp2.release(); c->d_bt_tmp2.release();
+  for (int i = 0; i < 10; ++i) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
   if (c->own_stream) cudaStreamDestroy(c->stream);
   delete c;
 }
@@ -476,6 +490,19 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
     threads = 256;
     ctas_per_sm = 2;
   }
+  // Few pairs: with less than one pair per resident CTA slot the SMs would run one or two four-warp CTAs each
+  // (a 16 x 200 kb slice of configs[4]: 111 pairs, 27 s). More warps per pair use them: at most one pair per SM ->
+  // 512 threads x 1 CTA, at most two -> 256 x 2. (--iterative launches 40 alignments at a time.)
+  if (c->auto_shape) {
+    const uint64_t per_sm = (n_pairs + (uint64_t)c->n_sm - 1) / (uint64_t)c->n_sm;
+    if (per_sm <= 1) {
+      threads = 512;
+      ctas_per_sm = 1;
+    } else if (per_sm <= 2 && threads < 256) {
+      threads = 256;
+      ctas_per_sm = 2;
+    }
+  }
   const size_t smem_rows = (size_t)(threads / 32) * STAGE_INTS * sizeof(int32_t);
   size_t smem_seqs = (size_t)2 * c->max_pk_words * 4;
   uint32_t smem_seq_words = c->max_pk_words;
@@ -529,7 +556,8 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
   // chunking: assume <= 1 run per 16 columns on average (3% divergence); overflow is detected and the
   // pairs that did not fit are re-run. Few large launches keep the end-of-launch tail (CTAs idling while
   // the last pairs finish) small against the launch.
-  uint64_t chunk = keep_runs ? n_pairs : std::max<uint64_t>(1, arena_cap / std::max<size_t>(1, runs_cap / 16));
+  // (in split mode the arena holds the pieces of the tasks and the joined list: twice the runs)
+  uint64_t chunk = keep_runs ? n_pairs : std::max<uint64_t>(1, arena_cap / std::max<size_t>(1, runs_cap / 8));
   chunk = std::min<uint64_t>(chunk, n_pairs);
   if (!keep_runs) chunk = std::min<uint64_t>(chunk, std::max<uint64_t>((uint64_t)grid * 64, 4096));
 
@@ -551,6 +579,33 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
   a.arena_cap = arena_cap;
   a.arena_head = c->d_scalars.p;
   a.next_pair = (unsigned int*)(c->d_scalars.p + 1);
+  a.leaf_T = 0;
+  a.tasks = nullptr;
+  a.task_pair = nullptr;
+  a.task_out = nullptr;
+  a.split = nullptr;
+  a.task_cap = 0;
+  a.task_count = (unsigned int*)(c->d_scalars.p + 3);
+  a.next_task = (unsigned int*)(c->d_scalars.p + 4);
+  // split mode: geometry of the one-warp kernel. Its ring rows must hold a sub-problem of score T: either search runs
+  // to about T/2 + scope, diagonals |k| <= score.
+  const int split_T = (c->split_T >= 250 && !getenv("SRGPU_NO_SPLIT")) ? c->split_T : 0;
+  const int sub_W = ((split_T + 2 * pen.scope + 128) + 63) & ~63;
+  const size_t sub_smem = (size_t)STAGE_INTS * sizeof(int32_t);
+  int sub_grid = 0;
+  uint64_t task_cap = 0;
+  if (split_T) {
+    int nb = 0;
+    cudaFuncSetAttribute(subalign_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sub_smem);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, subalign_kernel<32>, 32, sub_smem) != cudaSuccess || nb < 1) nb = 1;
+    sub_grid = c->n_sm * std::min(nb, 16);
+    const size_t sub_ring = (size_t)2 * (pen.scope + 1) * 5 * sub_W;
+    if ((rc = c->d_ring2.ensure((size_t)sub_grid * sub_ring))) return rc;
+    if ((rc = c->d_full2.ensure((size_t)sub_grid * 5 * cap * cap))) return rc;
+    if ((rc = c->d_full_meta2.ensure((size_t)sub_grid * cap * 5))) return rc;
+    if ((rc = c->d_runs_tmp2.ensure((size_t)sub_grid * runs_cap))) return rc;
+    if ((rc = c->d_bt_tmp2.ensure((size_t)sub_grid * runs_cap))) return rc;
+  }
 
   CK(cudaEventRecord(c->ev[0], c->stream));
   std::vector<PairOut> h_out;
@@ -622,11 +677,45 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
       a.W = curW;
       a.fixed_w = attempt > 0 ? 1 : 0;
       CK(cudaMemsetAsync(a.next_pair, 0, sizeof(unsigned int), c->stream));
+      // first attempt in split mode: align_kernel splits the big levels, subalign_kernel solves the sub-problems one
+      // warp each, assemble_kernel joins the pieces; re-runs (wider ring, arena) take the monolithic path
+      const bool split_now = split_T > 0 && attempt == 0;
+      a.leaf_T = 0;
+      if (split_now) {
+        task_cap = std::min<uint64_t>(std::max<uint64_t>((uint64_t)cn * 256, 65536), (uint64_t)1 << 26);
+        if ((rc = c->d_tasks.ensure(task_cap)) || (rc = c->d_task_pair.ensure(task_cap)) || (rc = c->d_task_out.ensure(task_cap)) ||
+            (rc = c->d_split.ensure(n_pairs)))
+          return rc;
+        a.leaf_T = split_T;
+        a.tasks = c->d_tasks.p;
+        a.task_pair = c->d_task_pair.p;
+        a.task_out = c->d_task_out.p;
+        a.split = c->d_split.p + first;
+        a.task_cap = (unsigned int)task_cap;
+        CK(cudaMemsetAsync(c->d_scalars.p + 3, 0, 2 * sizeof(unsigned long long), c->stream));
+      }
       CK(cudaEventRecord(c->ev[1], c->stream));
       cudaError_t e = launch_align(a, threads, ctas_per_sm, cur_grid, smem, c->stream);
       if (e != cudaSuccess) {
         g_err = std::string("align_kernel launch: ") + cudaGetErrorString(e);
         return SRGPU_E_CUDA;
+      }
+      if (split_now) {
+        CK(cudaEventRecord(c->ev[6], c->stream));
+        AlignArgs s2 = a;
+        s2.ring = c->d_ring2.p;
+        s2.ring_stride = (size_t)2 * (pen.scope + 1) * 5 * sub_W;
+        s2.W = sub_W;
+        s2.full = c->d_full2.p;
+        s2.full_meta = c->d_full_meta2.p;
+        s2.runs_tmp = c->d_runs_tmp2.p;
+        s2.bt_tmp = c->d_bt_tmp2.p;
+        subalign_kernel<32><<<sub_grid, 32, sub_smem, c->stream>>>(s2);
+        CK(cudaGetLastError());
+        CK(cudaEventRecord(c->ev[7], c->stream));
+        assemble_kernel<128><<<(unsigned)std::min<uint64_t>(cn, (uint64_t)c->n_sm * 8), 128, 0, c->stream>>>(a);
+        CK(cudaGetLastError());
+        c->stats.kernel_launches += 2;
       }
       CK(cudaEventRecord(c->ev[2], c->stream));
       c->stats.kernel_launches++;
@@ -637,6 +726,16 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
       float ms = 0;
       CK(cudaEventElapsedTime(&ms, c->ev[1], c->ev[2]));
       c->stats.align_ms += ms;
+      if (split_now && getenv("SRGPU_TRACE")) {
+        float m1 = 0, m2 = 0, m3 = 0;
+        cudaEventElapsedTime(&m1, c->ev[1], c->ev[6]);
+        cudaEventElapsedTime(&m2, c->ev[6], c->ev[7]);
+        cudaEventElapsedTime(&m3, c->ev[7], c->ev[2]);
+        unsigned int nt = 0;
+        cudaMemcpy(&nt, c->d_scalars.p + 3, 4, cudaMemcpyDeviceToHost);
+        fprintf(stderr, "[srgpu] split T=%d: align_kernel %.1f ms, subalign_kernel %.1f ms (%u tasks, grid %d, W %d), assemble_kernel %.2f ms\n",
+                split_T, m1, m2, nt, sub_grid, sub_W, m3);
+      }
       if (attempt == 0) {
         CK(cudaEventElapsedTime(&ms, c->ev[4], c->ev[5]));
         c->stats.orient_ms += ms;

@@ -111,6 +111,29 @@ struct AlignArgs {
   unsigned long long* arena_head;
   unsigned int* next_pair;
   const uint32_t* todo;  // optional indirection (retry lists); nullptr = identity
+  // split mode (leaf_T > 0): align_kernel only splits the big levels of the BiWFA recursion and emits the small
+  // sub-problems as tasks; subalign_kernel solves them one warp per task, assemble_kernel joins the pieces in order
+  int leaf_T;
+  struct Frame* tasks;          // [task_cap]
+  uint32_t* task_pair;          // [task_cap] slot of the pair (index into out[]) the task belongs to
+  struct TaskOut* task_out;     // [task_cap]
+  struct SplitRec* split;       // [n_pairs] by pair slot
+  unsigned int task_cap;
+  unsigned int* task_count;     // tasks emitted so far
+  unsigned int* next_task;      // subalign_kernel's work counter
+};
+
+struct TaskOut {
+  unsigned long long run_off;
+  unsigned long long cells;
+  uint32_t n_runs;
+  int32_t status, score;
+  int32_t pad;
+};
+struct SplitRec {
+  unsigned long long cells;  // cells of the levels align_kernel solved itself
+  uint32_t first_task, n_tasks;
+  int32_t status, score;     // score: level-0 score when align_kernel found the level-0 breakpoint, else INT32_MIN
 };
 
 static constexpr int ST_ARENA_OVERFLOW = 6;
@@ -251,7 +274,7 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
   if (staged && threadIdx.x == 0) mbar_init(&s_bar, 1);
 #ifdef WFA_PROFILE
   if (threadIdx.x == 0)
-    for (int i = 0; i < 20; ++i) sh.prof[i] = 0;
+    for (int i = 0; i < 20; ++i) sh.prof[i] = sh.prof2[i] = 0;
   const long long prof_start = clock64();
 #endif
   while (true) {
@@ -304,6 +327,40 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
     sv.lbits = lbits;
     // an alignment with `distance` unit edits costs at most max(x, cheapest one-base gap) per edit
     const long long per_edit = max(a.pen.x, min(a.pen.o1 + a.pen.e1, a.pen.o2 + a.pen.e2));
+    if (a.leaf_T > 0) {
+      // split mode: the run buffer of this CTA holds the leaves (32-byte frames) instead of runs
+      Frame* leaves = reinterpret_cast<Frame*>(ro.runs);
+      const uint32_t leaf_cap = (uint32_t)(((size_t)a.runs_cap * sizeof(uint32_t)) / sizeof(Frame));
+      const PairResult rs = wf_align_from(cx, sv, wf_root_frame((int)plen, (int)tlen), a.pen, ws, ro,
+                                          per_edit * (long long)orr.distance, leaves, leaf_cap, a.leaf_T);
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        int st = rs.status;
+        unsigned int first = 0;
+        if (st == ST_OK) {
+          first = atomicAdd(a.task_count, rs.n_runs);
+          if ((unsigned long long)first + rs.n_runs > a.task_cap) st = ST_ARENA_OVERFLOW;
+        }
+        sh.bcast[3] = st;
+        sh.bcast[4] = (int)first;
+        SplitRec sr;
+        sr.cells = sh.cells;
+        sr.first_task = first;
+        sr.n_tasks = st == ST_OK ? rs.n_runs : 0;
+        sr.status = st;
+        sr.score = rs.score;
+        a.split[pi] = sr;
+      }
+      __syncthreads();
+      if (sh.bcast[3] == ST_OK) {
+        const unsigned int first = (unsigned int)sh.bcast[4];
+        for (uint32_t i = threadIdx.x; i < rs.n_runs; i += THREADS) {
+          a.tasks[first + i] = leaves[i];
+          a.task_pair[first + i] = pi;
+        }
+      }
+      continue;
+    }
     const PairResult r = wf_align_pair(cx, sv, (int)plen, (int)tlen, a.pen, ws, ro, per_edit * (long long)orr.distance);
 #ifdef WFA_PROFILE
     if (threadIdx.x == 0) {
@@ -391,12 +448,243 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
            (int)blockIdx.x, pf[0], clock64() - prof_start, pf[1] / n, pf[2] / n, pf[3] / n, pf[4] / n, pf[5] / n, pf[7] / n);
     printf("[prof cta %d] passes %llu, chunks per pass %.2f, passes with <= 1 chunk per warp %.1f%%\n", (int)blockIdx.x, pf[16],
            pf[16] ? (double)pf[17] / pf[16] : 0.0, pf[16] ? 100.0 * pf[18] / pf[16] : 0.0);
+    {
+      const unsigned long long* q = sh.prof2;
+      printf("[prof cta %d] Mcycles: find_breakpoint L0 %.1f L1 %.1f L2 %.1f L3 %.1f L4+ %.1f | base case %.1f (%llu calls, backtrace %.1f) | "
+             "overlap %.1f, close phase %.1f (%llu overlap calls)\n", (int)blockIdx.x, q[0] / 1e6, q[1] / 1e6, q[2] / 1e6, q[3] / 1e6, q[4] / 1e6,
+             q[5] / 1e6, q[6], q[7] / 1e6, q[8] / 1e6, q[9] / 1e6, q[10]);
+      printf("[prof cta %d] Mcells: L0 %.1f L1 %.1f L2 %.1f L3 %.1f L4+ %.1f\n", (int)blockIdx.x, q[11] / 1e6, q[12] / 1e6, q[13] / 1e6,
+             q[14] / 1e6, q[15] / 1e6);
+    }
     printf("[prof cta %d] strand choice %llu cyc (sum of edit distances %llu), BiWFA %llu cyc\n", (int)blockIdx.x, pf[13], pf[15], pf[14]);
     printf("[prof cta %d] warp1 interior chunks %llu: compute %.0f cyc, extend %.0f cyc | warp0 fringe chunks %llu: %.0f cyc\n",
            (int)blockIdx.x, pf[8], pf[9] / (pf[8] ? (double)pf[8] : 1.0), pf[10] / (pf[8] ? (double)pf[8] : 1.0), pf[11],
            pf[12] / (pf[11] ? (double)pf[11] : 1.0));
   }
 #endif
+}
+
+// ---------------------------------------------------------------------------
+// Split mode, second launch: one task = one sub-problem (frame) of a pair, solved completely -- its own breakpoint
+// searches, recursion, base cases, backtraces -- by a one-warp CTA (persistent CTAs pulling tasks from a counter).
+// Narrow sub-problems leave three of four warps of a 128-thread CTA idle while every score step still pays three
+// CTA barriers (measured per pair at 50 kb / 1 %: recursion levels >= 2 and base cases were 51 % of the cycles for
+// 13 % of the cells, profiles/r02s_prof_phases.log); with a warp per task the "barriers" are warp-level and four
+// times as many sub-problems are in flight. Sequences are read from global memory; the runs of a task go to the arena.
+// ---------------------------------------------------------------------------
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS) subalign_kernel(AlignArgs a) {
+  extern __shared__ __align__(16) uint32_t s_dyn[];  // row staging buffers of the score step
+  __shared__ CtaShared sh;
+  __shared__ unsigned int s_task;
+  Ctx cx;
+  cx.sh = &sh;
+  cx.tid = threadIdx.x;
+  cx.nt = THREADS;
+  cx.parity = 0;
+  cx.stage = reinterpret_cast<int32_t*>(s_dyn);
+  const size_t b = blockIdx.x;
+  PairWorkspace ws;
+  ws.ring_f = a.ring + b * a.ring_stride;
+  ws.W = a.W;
+  ws.ring_r = ws.ring_f + (size_t)(a.pen.scope + 1) * 5 * a.W;
+  ws.full = a.full + b * a.full_stride;
+  ws.full_meta = a.full_meta + b * (size_t)a.cap * 5;
+  ws.cap = a.cap;
+  RunOut ro;
+  ro.runs = a.runs_tmp + b * (size_t)a.runs_cap;
+  ro.cap = a.runs_cap;
+  ro.bt = a.bt_tmp + b * (size_t)a.runs_cap;
+  ro.bt_cap = a.runs_cap;
+#ifdef WFA_PROFILE
+  if (threadIdx.x == 0)
+    for (int i = 0; i < 20; ++i) sh.prof[i] = sh.prof2[i] = 0;
+#endif
+  const unsigned int n_tasks = min(*a.task_count, a.task_cap);
+  while (true) {
+    __syncthreads();
+    if (threadIdx.x == 0) s_task = atomicAdd(a.next_task, 1u);
+    __syncthreads();
+    const unsigned int ti = s_task;
+    if (ti >= n_tasks) break;
+    const Frame f = a.tasks[ti];
+    const uint32_t pi = a.task_pair[ti];
+    const uint2 pr = a.pairs[pi];
+    const int is_rev = a.out[pi].is_reverse;
+    SeqView sv;
+    sv.p = (is_rev ? a.seqs.pk_rc : a.seqs.pk_fwd) + a.seqs.pk_off[pr.x];
+    sv.t = a.seqs.pk_fwd + a.seqs.pk_off[pr.y];
+    sv.lbits = a.seqs.lbits;
+    const long long per_edit = max(a.pen.x, min(a.pen.o1 + a.pen.e1, a.pen.o2 + a.pen.e2));
+    const PairResult r = wf_align_from(cx, sv, f, a.pen, ws, ro, per_edit * (long long)a.out[pi].edit_distance, nullptr, 0, 0);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      unsigned long long off = 0;
+      int st = r.status;
+      if (st == ST_OK) {
+        off = atomicAdd(a.arena_head, (unsigned long long)r.n_runs);
+        if (off + r.n_runs > a.arena_cap) st = ST_ARENA_OVERFLOW;
+      }
+      TaskOut to;
+      to.run_off = off;
+      to.cells = sh.cells;
+      to.n_runs = st == ST_OK ? r.n_runs : 0;
+      to.status = st;
+      to.score = r.score;
+      to.pad = 0;
+      a.task_out[ti] = to;
+      sh.bcast[3] = st;
+      sh.bcast64[0] = off;
+    }
+    __syncthreads();
+    if (sh.bcast[3] == ST_OK) {
+      const unsigned long long off = sh.bcast64[0];
+      for (uint32_t i = threadIdx.x; i < r.n_runs; i += THREADS) a.arena[off + i] = ro.runs[i];
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Split mode, third launch: one CTA per pair joins the run lists of its tasks in order into one canonical list
+// (adjacent runs never share an op: a piece whose first run continues the previous piece's last run is merged into
+// it, like cigar_append_forward does byte by byte, WFA2-lib/alignment/cigar.c:125-137), computes the CIGAR
+// statistics (allwave/src/alignment.rs:279-324) and the penalty, and writes the pair's result record.
+// ---------------------------------------------------------------------------
+static constexpr int ASM_MAX_TASKS = 1024;
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS) assemble_kernel(AlignArgs a) {
+  __shared__ unsigned long long s_src[ASM_MAX_TASKS];  // first copied run of the piece
+  __shared__ uint32_t s_dst[ASM_MAX_TASKS], s_cnt_t[ASM_MAX_TASKS];
+  __shared__ uint32_t s_patch_pos[ASM_MAX_TASKS], s_patch_val[ASM_MAX_TASKS];
+  __shared__ unsigned int s_cnt[8];
+  __shared__ unsigned long long s_off, s_cells;
+  __shared__ int s_st, s_score;
+  __shared__ uint32_t s_total, s_npatch;
+  for (uint32_t slot = blockIdx.x; slot < a.n_pairs; slot += gridDim.x) {
+    const uint32_t pi = a.todo ? a.todo[slot] : slot;
+    const SplitRec sr = a.split[pi];
+    __syncthreads();
+    if (threadIdx.x < 8) s_cnt[threadIdx.x] = 0;
+    if (threadIdx.x == 0) {
+      int st = sr.status;
+      int score = sr.score;
+      unsigned long long cells = sr.cells;
+      uint32_t out_n = 0, npatch = 0;
+      if (st == ST_OK && sr.n_tasks > (uint32_t)ASM_MAX_TASKS) st = ST_STACK_OVERFLOW;
+      if (st == ST_OK) {
+        bool have_last = false;
+        uint32_t last_pos = 0, last_val = 0;
+        for (uint32_t t = 0; t < sr.n_tasks; ++t) {
+          const TaskOut to = a.task_out[sr.first_task + t];
+          const Frame tf = a.tasks[sr.first_task + t];
+          cells += to.cells;
+          if (to.status != ST_OK) {
+            if (st == ST_OK || to.status == ST_WS_DIAG_OVERFLOW) st = to.status;
+            continue;
+          }
+          if (tf.level == 0) score = to.score;  // the whole pair was one task
+          s_cnt_t[t] = 0;
+          s_dst[t] = out_n;
+          s_src[t] = to.run_off;
+          if (to.n_runs == 0) continue;
+          const uint32_t r0 = a.arena[to.run_off];
+          uint32_t skip = 0;
+          if (have_last && ((r0 ^ last_val) & 3u) == 0) {
+            last_val += (r0 >> 2) << 2;
+            skip = 1;
+          }
+          if (to.n_runs - skip == 0) continue;  // the whole piece went into the open run
+          if (have_last) {
+            s_patch_pos[npatch] = last_pos;
+            s_patch_val[npatch++] = last_val;
+          }
+          s_src[t] = to.run_off + skip;
+          s_cnt_t[t] = to.n_runs - skip;
+          out_n += to.n_runs - skip;
+          last_pos = out_n - 1;
+          last_val = a.arena[to.run_off + to.n_runs - 1];
+          have_last = true;
+        }
+        if (have_last) {
+          s_patch_pos[npatch] = last_pos;
+          s_patch_val[npatch++] = last_val;
+        }
+      }
+      unsigned long long off = 0;
+      if (st == ST_OK) {
+        off = atomicAdd(a.arena_head, (unsigned long long)out_n);
+        if (off + out_n > a.arena_cap) st = ST_ARENA_OVERFLOW;
+      }
+      s_st = st;
+      s_score = score;
+      s_cells = cells;
+      s_off = off;
+      s_total = out_n;
+      s_npatch = npatch;
+    }
+    __syncthreads();
+    const int st = s_st;
+    const unsigned long long off = s_off;
+    if (st == ST_OK) {
+      for (uint32_t t = 0; t < sr.n_tasks; ++t) {
+        const uint32_t n = s_cnt_t[t], d = s_dst[t];
+        const unsigned long long src = s_src[t];
+        for (uint32_t i = threadIdx.x; i < n; i += THREADS) a.arena[off + d + i] = a.arena[src + i];
+      }
+      __syncthreads();
+      for (uint32_t i = threadIdx.x; i < s_npatch; i += THREADS) a.arena[off + s_patch_pos[i]] = s_patch_val[i];
+      __syncthreads();
+      uint32_t c_m = 0, c_x = 0, c_i = 0, c_d = 0, c_pen = 0;
+      for (uint32_t i = threadIdx.x; i < s_total; i += THREADS) {
+        const uint32_t run = a.arena[off + i];
+        const uint32_t op = run & 3u, len = run >> 2;
+        if (op == OP_M) {
+          c_m += len;
+        } else if (op == OP_X) {
+          c_x += len;
+          c_pen += len * (uint32_t)a.pen.x;
+        } else {
+          if (op == OP_I) c_i += len; else c_d += len;
+          const uint32_t s1 = (uint32_t)a.pen.o1 + (uint32_t)a.pen.e1 * len;
+          const uint32_t s2 = (uint32_t)a.pen.o2 + (uint32_t)a.pen.e2 * len;
+          c_pen += s1 < s2 ? s1 : s2;
+        }
+      }
+      c_m = __reduce_add_sync(0xffffffffu, c_m);
+      c_x = __reduce_add_sync(0xffffffffu, c_x);
+      c_i = __reduce_add_sync(0xffffffffu, c_i);
+      c_d = __reduce_add_sync(0xffffffffu, c_d);
+      c_pen = __reduce_add_sync(0xffffffffu, c_pen);
+      if ((threadIdx.x & 31) == 0) {
+        atomicAdd(&s_cnt[0], c_m);
+        atomicAdd(&s_cnt[1], c_x);
+        atomicAdd(&s_cnt[2], c_i);
+        atomicAdd(&s_cnt[3], c_d);
+        atomicAdd(&s_cnt[4], c_pen);
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const uint2 pr = a.pairs[pi];
+      PairOut o;
+      o.q = pr.x;
+      o.t = pr.y;
+      o.is_reverse = a.out[pi].is_reverse;
+      o.edit_distance = a.out[pi].edit_distance;
+      o.ocells = a.out[pi].ocells;
+      o.status = st;
+      o.score = (st == ST_OK) ? s_score : INT32_MAX;
+      o.penalty = (int32_t)s_cnt[4];
+      o.num_matches = s_cnt[0];
+      o.n_mismatch = s_cnt[1];
+      o.n_ins = s_cnt[2];
+      o.n_del = s_cnt[3];
+      o.n_runs = (st == ST_OK) ? s_total : 0;
+      o.run_off = off;
+      o.cells = s_cells;
+      a.out[pi] = o;
+    }
+  }
 }
 
 // ---------------------------------------------------------------------------

@@ -140,7 +140,11 @@ struct WfStore {
     const int t = cur_slot - (cur_s - s);
     return t < 0 ? t + scope : t;
   }
+#ifdef SRGPU_EXP_SHALLOW  // measurement build only: gap components in a 3-slot ring (valid in the far phase only)
+  WFA_FN int off_of(int s, int c) const { return ((c == C_M ? slot(s) : (s % 3)) * 5 + c) * W + (W >> 1); }
+#else
   WFA_FN int off_of(int s, int c) const { return (slot(s) * 5 + c) * W + (W >> 1); }  // modular rows only
+#endif
   WFA_FN int32_t* row_of_slot(int sl, int c) const { return base + (uint32_t)((sl * 5 + c) * W + (W >> 1)); }
   WFA_FN int32_t* row(int s, int c) const {
     if (modular) {
@@ -195,6 +199,8 @@ struct CtaShared {
   unsigned long long ocells;  // orientation (unit-cost) cells
 #ifdef WFA_PROFILE
   unsigned long long prof[20];  // cycle counters of thread 0 (development only)
+  unsigned long long prof2[20]; // phase breakdown: [0..4] find_breakpoint cycles by level (4 = deeper), [5] base case, [6] base calls,
+                                // [7] backtrace, [8] overlap, [9] close phase, [10] close steps, [11..15] cells by level
 #endif
 };
 
@@ -1675,6 +1681,12 @@ WFA_FN int wf_find_breakpoint(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
   StepOut parked_out = o;
   while (true) {
     if ((long long)score_f + score_r > score_bound) return 3;
+#ifdef SRGPU_EXP_ABORT_CLOSE  // measurement build only: stop every pair where the close phase would begin
+    if (!close && fwd_max_ak + rev_max_ak >= max_antidiagonal) return 4;
+#endif
+#ifdef WFA_PROFILE
+    if (!close && fwd_max_ak + rev_max_ak >= max_antidiagonal && cx.tid == 0) cx.sh->prof2[16] = clock64();
+#endif
     if (!close && fwd_max_ak + rev_max_ak >= max_antidiagonal) close = true;
     const bool tf = turn_forward;
     const bool dual = !close && tf;
@@ -1685,7 +1697,14 @@ WFA_FN int wf_find_breakpoint(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
       if (min_own + oth - gap_opening >= cx.sh->bp.score) break;
       // the wavefront that moved last is searched against the scope of the one about to move
       const Dir a = tf ? dr : df, b = tf ? df : dr;
+      PROF_T(tov0);
       wf_overlap(cx, a, b, pen, oth, own, !tf);
+#ifdef WFA_PROFILE
+      if (cx.tid == 0) {
+        cx.sh->prof2[8] += clock64() - tov0;
+        cx.sh->prof2[10] += 1;
+      }
+#endif
     }
     StepOut2 o2;
     o2.f = o;
@@ -1701,6 +1720,9 @@ WFA_FN int wf_find_breakpoint(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
         return 1;
       }
       turn_forward = false;
+#ifdef SRGPU_EXP_ABORT_CLOSE
+      if (dual && fwd_max_ak + rev_max_ak >= max_antidiagonal) return 4;
+#endif
       if (dual && fwd_max_ak + rev_max_ak >= max_antidiagonal) {
         // closeness reached between the two halves: replay the reverse turn in reference order
         parked = true;
@@ -1879,7 +1901,11 @@ WFA_FN int wf_base(Ctx& cx, Dir& db, const Penalties& pen, const RunOut& ro) {
   }
   cta_sync();
   if (cx.tid == 0) {
+    PROF_T(tbt0);
     const bool ok = wf_backtrace(cx.sh, ro, db.st, pen, db.plen, db.tlen, db.cbegin, db.cend, score);
+#ifdef WFA_PROFILE
+    cx.sh->prof2[7] += clock64() - tbt0;
+#endif
     cx.sh->bcast[1] = ok ? 1 : 0;
     cx.sh->bcast[2] = (int)cx.sh->n_runs;
     if (ok && cx.sh->n_runs + cx.sh->bt_n > ro.cap) cx.sh->bcast[1] = 0;
@@ -1953,8 +1979,14 @@ WFA_FN void set_dirs(Dir& df, Dir& dr, Dir& db, const SeqView& sv, const Frame& 
   db.cend = f.cend;
 }
 
-WFA_FN PairResult wf_align_pair(Ctx& cx, const SeqView& sv, int plen, int tlen, const Penalties& pen,
-                                const PairWorkspace& ws, const RunOut& ro, long long score_hint = INT64_MAX) {
+// Driver over the BiWFA recursion starting from frame f0 (the whole pair, or one sub-problem of it: the two halves
+// after a breakpoint are independent, WFA/wavefront_bialign.c:1193-1212, only the order of their CIGAR pieces
+// matters). SPLIT MODE (leaves != nullptr): frames that are trivial, whose score_remaining is at most leaf_T
+// (>= 250, so every base case is one), or whose search ended by reaching the end are not solved but emitted, in
+// left-to-right order, into leaves[]; res.n_runs is then the number of leaves. A one-warp-per-task kernel solves them
+// and the pieces are joined in order afterwards (kernels.cuh: subalign_kernel, assemble_kernel).
+WFA_FN PairResult wf_align_from(Ctx& cx, const SeqView& sv, const Frame f0, const Penalties& pen, const PairWorkspace& ws,
+                                const RunOut& ro, long long score_hint, Frame* leaves, uint32_t leaf_cap, int leaf_T) {
   CtaShared* sh = cx.sh;
   PairResult res;
   res.status = ST_OK;
@@ -1989,20 +2021,15 @@ WFA_FN PairResult wf_align_pair(Ctx& cx, const SeqView& sv, int plen, int tlen, 
     sh->cells = 0;
     sh->sp = 0;
     sh->status = ST_OK;
-    Frame f;
-    f.pb = 0;
-    f.pe = plen;
-    f.tb = 0;
-    f.te = tlen;
-    f.cbegin = C_M;
-    f.cend = C_M;
-    // WFA/wavefront_bialign.c:1279-1283
-    f.score_remaining = (imax(plen, tlen) <= 100) ? 0 : INT32_MAX;
-    f.level = 0;
-    sh->stack[sh->sp++] = f;
+    sh->stack[sh->sp++] = f0;
   }
   cta_sync();
   int level0_score = INT32_MIN;
+  const bool split = leaves != nullptr;
+  auto emit_leaf = [&](const Frame& lf) {  // thread 0
+    if (sh->n_runs >= leaf_cap) sh->status = ST_WS_RUNS_OVERFLOW;
+    else leaves[sh->n_runs++] = lf;
+  };
   while (true) {
     cta_sync();
     if (sh->sp == 0 || sh->status != ST_OK) break;
@@ -2011,6 +2038,10 @@ WFA_FN PairResult wf_align_pair(Ctx& cx, const SeqView& sv, int plen, int tlen, 
     if (cx.tid == 0) sh->sp--;
     const int fp = f.pe - f.pb, ft = f.te - f.tb;
     int st = ST_OK;
+    if (split && (ft == 0 || fp == 0 || f.score_remaining <= leaf_T)) {
+      if (cx.tid == 0) emit_leaf(f);
+      continue;
+    }
     if (ft == 0) {
       if (cx.tid == 0 && !runs_push(sh, ro, OP_D, (uint32_t)fp)) sh->status = ST_WS_RUNS_OVERFLOW;
       continue;
@@ -2020,13 +2051,35 @@ WFA_FN PairResult wf_align_pair(Ctx& cx, const SeqView& sv, int plen, int tlen, 
     }
     set_dirs(df, dr, db, sv, f);
     if (f.score_remaining <= 250) {  // WF_BIALIGN_FALLBACK_MIN_SCORE
+      PROF_T(tb0);
       st = wf_base(cx, db, pen, ro);
+#ifdef WFA_PROFILE
+      if (cx.tid == 0) {
+        sh->prof2[5] += clock64() - tb0;
+        sh->prof2[6] += 1;
+      }
+#endif
       if (st != ST_OK && cx.tid == 0) sh->status = st;
       continue;
     }
     int score_reached = 0;
+#ifdef WFA_PROFILE
+    const long long tfb0 = clock64();
+    const unsigned long long cells0 = sh->cells;
+    if (cx.tid == 0) sh->prof2[16] = 0;
+#endif
     const int r = wf_find_breakpoint(cx, df, dr, pen, &score_reached,
                                      f.level == 0 ? score_hint : (long long)f.score_remaining);
+#ifdef WFA_PROFILE
+    cta_sync();
+    if (cx.tid == 0) {
+      const long long tfb1 = clock64();
+      const int lb = f.level < 4 ? f.level : 4;
+      sh->prof2[lb] += tfb1 - tfb0;
+      sh->prof2[11 + lb] += sh->cells - cells0;
+      if (sh->prof2[16]) sh->prof2[9] += tfb1 - (long long)sh->prof2[16];
+    }
+#endif
     if (r == 2) {
       if (cx.tid == 0) sh->status = ST_WS_DIAG_OVERFLOW;
       continue;
@@ -2035,9 +2088,17 @@ WFA_FN PairResult wf_align_pair(Ctx& cx, const SeqView& sv, int plen, int tlen, 
       if (cx.tid == 0) sh->status = ST_RUNAWAY;
       continue;
     }
+#ifdef SRGPU_EXP_ABORT_CLOSE
+    if (r == 4) {
+      if (cx.tid == 0) sh->status = ST_UNATTAINABLE;
+      continue;
+    }
+#endif
     if (r == 1) {
       // WFA/wavefront_bialign.c:1083-1112: recover through the base case when cheap enough
-      if (score_reached <= 500) {  // WF_BIALIGN_RECOVERY_MIN_SCORE
+      if (score_reached <= 500 && split) {  // the task repeats this (cheap: <= 500 scores) search and recovers there
+        if (cx.tid == 0) emit_leaf(f);
+      } else if (score_reached <= 500) {  // WF_BIALIGN_RECOVERY_MIN_SCORE
         st = wf_base(cx, db, pen, ro);
         if (st != ST_OK && cx.tid == 0) sh->status = st;
       } else if (cx.tid == 0) {
@@ -2051,7 +2112,7 @@ WFA_FN PairResult wf_align_pair(Ctx& cx, const SeqView& sv, int plen, int tlen, 
     if (f.level == 0) {
       // WFA/wavefront_bialign.c:1214-1219 -> wavefront_compute_classic_score (WFA/wavefront_compute.c:108-120):
       // -score for match == 0, else WF_SCORE_TO_SW_SCORE = (swg_match * (plen + tlen) - score) / 2
-      level0_score = pen.match == 0 ? -bp.score : ((-pen.match) * (plen + tlen) - bp.score) / 2;
+      level0_score = pen.match == 0 ? -bp.score : ((-pen.match) * ((f.pe - f.pb) + (f.te - f.tb)) - bp.score) / 2;
     }
     cta_sync();
     if (cx.tid == 0) {
@@ -2086,6 +2147,25 @@ WFA_FN PairResult wf_align_pair(Ctx& cx, const SeqView& sv, int plen, int tlen, 
   res.score = level0_score;
   res.n_runs = sh->n_runs;
   return res;
+}
+
+WFA_FN Frame wf_root_frame(int plen, int tlen) {
+  Frame f;
+  f.pb = 0;
+  f.pe = plen;
+  f.tb = 0;
+  f.te = tlen;
+  f.cbegin = C_M;
+  f.cend = C_M;
+  // WFA/wavefront_bialign.c:1279-1283
+  f.score_remaining = (imax(plen, tlen) <= 100) ? 0 : INT32_MAX;
+  f.level = 0;
+  return f;
+}
+
+WFA_FN PairResult wf_align_pair(Ctx& cx, const SeqView& sv, int plen, int tlen, const Penalties& pen,
+                                const PairWorkspace& ws, const RunOut& ro, long long score_hint = INT64_MAX) {
+  return wf_align_from(cx, sv, wf_root_frame(plen, tlen), pen, ws, ro, score_hint, nullptr, 0, 0);
 }
 
 }  // namespace srb
