@@ -173,6 +173,32 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+#ifdef WFA_PROFILE
+// cycle counters of one CTA (measurement build only)
+__device__ __noinline__ void prof_print(const CtaShared& sh, long long prof_start, const char* tag) {
+  printf("[prof %s]\n", tag);
+    const unsigned long long* pf = sh.prof;
+    const double n = pf[0] ? (double)pf[0] : 1.0;
+    printf("[prof cta %d] ring steps %llu  total cyc %lld | per step: top-barrier %.0f  setup %.0f  loop %.0f  finish %.0f  "
+           "(barrier wait %.0f) | avg width %.0f\n",
+           (int)blockIdx.x, pf[0], clock64() - prof_start, pf[1] / n, pf[2] / n, pf[3] / n, pf[4] / n, pf[5] / n, pf[7] / n);
+    printf("[prof cta %d] passes %llu, chunks per pass %.2f, passes with <= 1 chunk per warp %.1f%%\n", (int)blockIdx.x, pf[16],
+           pf[16] ? (double)pf[17] / pf[16] : 0.0, pf[16] ? 100.0 * pf[18] / pf[16] : 0.0);
+    {
+      const unsigned long long* q = sh.prof2;
+      printf("[prof cta %d] Mcycles: find_breakpoint L0 %.1f L1 %.1f L2 %.1f L3 %.1f L4+ %.1f | base case %.1f (%llu calls, backtrace %.1f) | "
+             "overlap %.1f, close phase %.1f (%llu overlap calls)\n", (int)blockIdx.x, q[0] / 1e6, q[1] / 1e6, q[2] / 1e6, q[3] / 1e6, q[4] / 1e6,
+             q[5] / 1e6, q[6], q[7] / 1e6, q[8] / 1e6, q[9] / 1e6, q[10]);
+      printf("[prof cta %d] Mcells: L0 %.1f L1 %.1f L2 %.1f L3 %.1f L4+ %.1f\n", (int)blockIdx.x, q[11] / 1e6, q[12] / 1e6, q[13] / 1e6,
+             q[14] / 1e6, q[15] / 1e6);
+    }
+    printf("[prof cta %d] strand choice %llu cyc (sum of edit distances %llu), BiWFA %llu cyc\n", (int)blockIdx.x, pf[13], pf[15], pf[14]);
+    printf("[prof cta %d] warp1 interior chunks %llu: compute %.0f cyc, extend %.0f cyc | warp0 fringe chunks %llu: %.0f cyc\n",
+           (int)blockIdx.x, pf[8], pf[9] / (pf[8] ? (double)pf[8] : 1.0), pf[10] / (pf[8] ? (double)pf[8] : 1.0), pf[11],
+           pf[12] / (pf[11] ? (double)pf[11] : 1.0));
+}
+#endif
+
 // ---------------------------------------------------------------------------
 // Strand choice for every pair of a launch (allwave/src/alignment.rs:24-30,148-171), one pair per
 // CTA, persistent CTAs. It runs as its own launch because it needs three staged sequences (query
@@ -440,27 +466,7 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
     }
   }
 #ifdef WFA_PROFILE
-  if (threadIdx.x == 0 && blockIdx.x < 4) {
-    const unsigned long long* pf = sh.prof;
-    const double n = pf[0] ? (double)pf[0] : 1.0;
-    printf("[prof cta %d] ring steps %llu  total cyc %lld | per step: top-barrier %.0f  setup %.0f  loop %.0f  finish %.0f  "
-           "(barrier wait %.0f) | avg width %.0f\n",
-           (int)blockIdx.x, pf[0], clock64() - prof_start, pf[1] / n, pf[2] / n, pf[3] / n, pf[4] / n, pf[5] / n, pf[7] / n);
-    printf("[prof cta %d] passes %llu, chunks per pass %.2f, passes with <= 1 chunk per warp %.1f%%\n", (int)blockIdx.x, pf[16],
-           pf[16] ? (double)pf[17] / pf[16] : 0.0, pf[16] ? 100.0 * pf[18] / pf[16] : 0.0);
-    {
-      const unsigned long long* q = sh.prof2;
-      printf("[prof cta %d] Mcycles: find_breakpoint L0 %.1f L1 %.1f L2 %.1f L3 %.1f L4+ %.1f | base case %.1f (%llu calls, backtrace %.1f) | "
-             "overlap %.1f, close phase %.1f (%llu overlap calls)\n", (int)blockIdx.x, q[0] / 1e6, q[1] / 1e6, q[2] / 1e6, q[3] / 1e6, q[4] / 1e6,
-             q[5] / 1e6, q[6], q[7] / 1e6, q[8] / 1e6, q[9] / 1e6, q[10]);
-      printf("[prof cta %d] Mcells: L0 %.1f L1 %.1f L2 %.1f L3 %.1f L4+ %.1f\n", (int)blockIdx.x, q[11] / 1e6, q[12] / 1e6, q[13] / 1e6,
-             q[14] / 1e6, q[15] / 1e6);
-    }
-    printf("[prof cta %d] strand choice %llu cyc (sum of edit distances %llu), BiWFA %llu cyc\n", (int)blockIdx.x, pf[13], pf[15], pf[14]);
-    printf("[prof cta %d] warp1 interior chunks %llu: compute %.0f cyc, extend %.0f cyc | warp0 fringe chunks %llu: %.0f cyc\n",
-           (int)blockIdx.x, pf[8], pf[9] / (pf[8] ? (double)pf[8] : 1.0), pf[10] / (pf[8] ? (double)pf[8] : 1.0), pf[11],
-           pf[12] / (pf[11] ? (double)pf[11] : 1.0));
-  }
+  if (threadIdx.x == 0 && blockIdx.x < 4) prof_print(sh, prof_start, "align_kernel");
 #endif
 }
 
@@ -499,6 +505,7 @@ __global__ void __launch_bounds__(THREADS) subalign_kernel(AlignArgs a) {
 #ifdef WFA_PROFILE
   if (threadIdx.x == 0)
     for (int i = 0; i < 20; ++i) sh.prof[i] = sh.prof2[i] = 0;
+  const long long prof_start = clock64();
 #endif
   const unsigned int n_tasks = min(*a.task_count, a.task_cap);
   while (true) {
@@ -542,6 +549,9 @@ __global__ void __launch_bounds__(THREADS) subalign_kernel(AlignArgs a) {
       for (uint32_t i = threadIdx.x; i < r.n_runs; i += THREADS) a.arena[off + i] = ro.runs[i];
     }
   }
+#ifdef WFA_PROFILE
+  if (threadIdx.x == 0 && blockIdx.x < 4) prof_print(sh, prof_start, "subalign_kernel");
+#endif
 }
 
 // ---------------------------------------------------------------------------
