@@ -118,6 +118,11 @@ void* srgpu_ctx_stream(srgpu_ctx* ctx);
 /* Tunables: threads per CTA (multiple of 32), CTAs per SM, initial ring width in diagonals
  * (0 = automatic). */
 int srgpu_ctx_configure(srgpu_ctx* ctx, int threads, int ctas_per_sm, int ring_diagonals);
+/* Tunable of the alignment launches (no reference counterpart): BiWFA sub-problems whose remaining score is at
+ * most `split_score` are finished by one-warp CTAs in a second launch and joined by a third; 0 keeps every
+ * pair in one CTA from start to end ("monolithic"), values below 250 (the reference's base-case threshold,
+ * WFA2-lib/wavefront/wavefront_bialign.c) are refused. Results do not depend on it. Default 1000. */
+int srgpu_ctx_set_split(srgpu_ctx* ctx, int split_score);
 int srgpu_ctx_stats(srgpu_ctx* ctx, srgpu_stats* out);
 
 /* Upload the sequence set (host -> HBM). Replaces the `&[Sequence]` argument of

@@ -18,7 +18,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 # every symbol include/seqrush_b200.h declares (checked by tests/test_abi.py)
 EXPORTS = [
     "srgpu_last_error", "srgpu_ctx_create", "srgpu_ctx_destroy", "srgpu_ctx_synchronize", "srgpu_ctx_stream",
-    "srgpu_ctx_configure", "srgpu_uf_compress_async", "srgpu_uf_merge_gathered",
+    "srgpu_ctx_configure", "srgpu_ctx_set_split", "srgpu_uf_compress_async", "srgpu_uf_merge_gathered",
     "srgpu_ctx_stats", "srgpu_set_sequences", "srgpu_total_length", "srgpu_align_pairs", "srgpu_free",
     "srgpu_align_and_unite", "srgpu_align_and_unite_device", "srgpu_align_pairs_and_unite",
     "srgpu_process_alignment", "srgpu_process_alignments", "srgpu_uf_new",
@@ -116,6 +116,7 @@ def lib():
     L.srgpu_ctx_destroy.restype = None
     L.srgpu_ctx_synchronize.argtypes = [vp]
     L.srgpu_ctx_configure.argtypes = [vp, i32, i32, i32]
+    L.srgpu_ctx_set_split.argtypes = [vp, i32]
     L.srgpu_ctx_stats.argtypes = [vp, C.POINTER(Stats)]
     L.srgpu_set_sequences.argtypes = [vp, C.POINTER(SeqView), u32]
     L.srgpu_total_length.argtypes = [vp]

@@ -34,6 +34,10 @@ class Context:
     def configure(self, threads=0, ctas_per_sm=0, ring_diagonals=-1):
         _lib.check(_lib.lib().srgpu_ctx_configure(self._h, threads, ctas_per_sm, ring_diagonals))
 
+    def set_split(self, split_score: int):
+        """0: every pair stays in one CTA; >= 250: sub-problems at or below that score go to one-warp CTAs."""
+        _lib.check(_lib.lib().srgpu_ctx_set_split(self._h, int(split_score)))
+
     def stream_ptr(self) -> int:
         """cudaStream_t of every launch of this context."""
         return int(_lib.lib().srgpu_ctx_stream(self._h) or 0)

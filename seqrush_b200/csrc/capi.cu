@@ -102,6 +102,9 @@ struct srgpu_ctx {
   DevBuf<uint32_t> d_arena, d_todo;
   DevBuf<unsigned long long> d_scalars;  // [0] arena_head, [1] next_pair(uint), [2] max edit distance, [3] task_count, [4] next_task
   // split mode: tasks (sub-problems) and the workspaces of the one-warp kernel that solves them
+  int sub_ctas_per_sm = SUB_CTAS;  // one-warp CTAs per SM of subalign_kernel (SRGPU_SUB_CTAS lowers it). 1500-pair c2 slice:
+                                   // 13 -> 231.6 ms, 16 -> 210.7 ms; a 96-register build at 20 -> 216.5 ms (profiles/r03a_*): the
+                                   // kernel is bound by instruction fetch (profiles/r02z_*), not by warps in flight
   int split_T = 1000;  // sub-problems whose score_remaining is at most this go to subalign_kernel (0: monolithic); SRGPU_SPLIT_T.
                        // 1500-pair slices: c2 840 ms monolithic, 728 / 740 / 766 / 831 at T = 500 / 1000 / 1900 / 3900; 100 kb 2837 -> 2756 / 2737 / 2717
                        // (profiles/r02t_*, r02u_*, r02v_*)
@@ -174,6 +177,7 @@ extern "C" int srgpu_ctx_create(int device, void* stream, srgpu_ctx** out) {
   if (const char* e = getenv("SRGPU_SMEM_BUDGET")) c->smem_budget = atoi(e);  // tuning: 0 = never stage sequences
   if (const char* e = getenv("SRGPU_SPLIT_T")) c->split_T = atoi(e);
   if (const char* e = getenv("SRGPU_ORIENT_CTAS")) c->orient_ctas_per_sm = std::max(1, atoi(e));
+  if (const char* e = getenv("SRGPU_SUB_CTAS")) c->sub_ctas_per_sm = std::max(1, atoi(e));
   if (const char* e = getenv("SRGPU_STAGE_SEQS")) c->stage_seqs = atoi(e) != 0 ? 1 : 0;
   *out = c;
   return SRGPU_OK;
@@ -224,6 +228,17 @@ extern "C" int srgpu_ctx_configure(srgpu_ctx* c, int threads, int ctas_per_sm, i
     c->auto_shape = false;
   }
   if (ring_diagonals >= 0) c->ring_diagonals = ring_diagonals;
+  return SRGPU_OK;
+}
+
+extern "C" int srgpu_ctx_set_split(srgpu_ctx* c, int split_score) {
+  if (!c) return SRGPU_E_ARG;
+  if (split_score != 0 && split_score < 250) {
+    g_err = "split_score must be 0 (monolithic) or at least 250";
+    return SRGPU_E_ARG;
+  }
+  std::lock_guard<std::mutex> lk(c->mu);
+  c->split_T = split_score;
   return SRGPU_OK;
 }
 
@@ -507,7 +522,7 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
   size_t smem_seqs = (size_t)2 * c->max_pk_words * 4;
   uint32_t smem_seq_words = c->max_pk_words;
   {
-    const size_t per_sm = 227 * 1024, static_smem = 13 * 1024 + 1024;  // CtaShared + the per-CTA reservation
+    const size_t per_sm = 227 * 1024, static_smem = 13 * 1024 + 1024;  // CtaShared + CtaTables + the per-CTA reservation
     const bool fits = (static_smem + smem_rows + smem_seqs) * (size_t)ctas_per_sm <= per_sm;
     const bool want = c->stage_seqs < 0 ? fits : c->stage_seqs != 0;
     if (!want || smem_seqs > (size_t)c->smem_budget || static_smem + smem_rows + smem_seqs > per_sm) {
@@ -589,16 +604,23 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
   a.next_task = (unsigned int*)(c->d_scalars.p + 4);
   // split mode: geometry of the one-warp kernel. Its ring rows must hold a sub-problem of score T: either search runs
   // to about T/2 + scope, diagonals |k| <= score.
-  const int split_T = (c->split_T >= 250 && !getenv("SRGPU_NO_SPLIT")) ? c->split_T : 0;
-  const int sub_W = ((split_T + 2 * pen.scope + 128) + 63) & ~63;
+  const int split_T = (c->split_T >= 250 && !getenv("SRGPU_NO_SPLIT") && pen.scope + 1 <= SUB_SLOTS) ? c->split_T : 0;
+  // (never wider than a full row, and within a 24 GB budget over the grid: a task that overflows its ring sends the
+  // pair to the monolithic retry)
+  int sub_W = ((int)std::min<long long>((long long)split_T + 2 * pen.scope + 128, (long long)fullW) + 63) & ~63;
   const size_t sub_smem = (size_t)STAGE_INTS * sizeof(int32_t);
   int sub_grid = 0;
   uint64_t task_cap = 0;
   if (split_T) {
     int nb = 0;
-    cudaFuncSetAttribute(subalign_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sub_smem);
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, subalign_kernel<32>, 32, sub_smem) != cudaSuccess || nb < 1) nb = 1;
-    sub_grid = c->n_sm * std::min(nb, 16);
+    cudaFuncSetAttribute(subalign_kernel<32, SUB_CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sub_smem);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, subalign_kernel<32, SUB_CTAS>, 32, sub_smem) != cudaSuccess || nb < 1) nb = 1;
+    sub_grid = c->n_sm * std::min(nb, c->sub_ctas_per_sm);
+    {
+      const size_t budget = (size_t)24 << 30, per_diag = (size_t)2 * (pen.scope + 1) * 5 * sizeof(int32_t);
+      const size_t fit = budget / (per_diag * (size_t)sub_grid);
+      if ((size_t)sub_W > fit) sub_W = (int)std::max<size_t>(fit & ~(size_t)63, 1024);
+    }
     const size_t sub_ring = (size_t)2 * (pen.scope + 1) * 5 * sub_W;
     if ((rc = c->d_ring2.ensure((size_t)sub_grid * sub_ring))) return rc;
     if ((rc = c->d_full2.ensure((size_t)sub_grid * 5 * cap * cap))) return rc;
@@ -710,7 +732,7 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
         s2.full_meta = c->d_full_meta2.p;
         s2.runs_tmp = c->d_runs_tmp2.p;
         s2.bt_tmp = c->d_bt_tmp2.p;
-        subalign_kernel<32><<<sub_grid, 32, sub_smem, c->stream>>>(s2);
+        subalign_kernel<32, SUB_CTAS><<<sub_grid, 32, sub_smem, c->stream>>>(s2);
         CK(cudaGetLastError());
         CK(cudaEventRecord(c->ev[7], c->stream));
         assemble_kernel<128><<<(unsigned)std::min<uint64_t>(cn, (uint64_t)c->n_sm * 8), 128, 0, c->stream>>>(a);

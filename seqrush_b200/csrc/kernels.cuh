@@ -274,9 +274,11 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
   // sequences are read from global memory through L1) followed by the per-warp row staging buffers of the score step
   extern __shared__ __align__(16) uint32_t s_seq[];
   __shared__ CtaShared sh;
+  __shared__ CtaTables<MAX_SCOPE, STACK_MAX> s_tables;
   __shared__ unsigned int s_pair;
   __shared__ unsigned int s_cnt[8];
   __shared__ __align__(8) uint64_t s_bar;
+  if (threadIdx.x == 0) cta_bind(&sh, &s_tables);
   Ctx cx;
   cx.sh = &sh;
   cx.tid = threadIdx.x;
@@ -478,11 +480,16 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
 // 13 % of the cells, profiles/r02s_prof_phases.log); with a warp per task the "barriers" are warp-level and four
 // times as many sub-problems are in flight. Sequences are read from global memory; the runs of a task go to the arena.
 // ---------------------------------------------------------------------------
-template <int THREADS>
-__global__ void __launch_bounds__(THREADS) subalign_kernel(AlignArgs a) {
+static constexpr int SUB_SLOTS = 32;  // ring slots of the one-warp kernel (scope + 1 <= 32, else the launch stays monolithic)
+static constexpr int SUB_CTAS = 16;   // one-warp CTAs per SM (128 registers; the tables below keep shared memory at 10 KB per CTA)
+static constexpr int SUB_STACK = 32;  // a task starts below split_T: a few levels deep at most; overflow -> monolithic retry
+template <int THREADS, int MIN_CTAS>
+__global__ void __launch_bounds__(THREADS, MIN_CTAS) subalign_kernel(AlignArgs a) {
   extern __shared__ __align__(16) uint32_t s_dyn[];  // row staging buffers of the score step
   __shared__ CtaShared sh;
+  __shared__ CtaTables<SUB_SLOTS, SUB_STACK> s_tables;
   __shared__ unsigned int s_task;
+  if (threadIdx.x == 0) cta_bind(&sh, &s_tables);
   Ctx cx;
   cx.sh = &sh;
   cx.tid = threadIdx.x;
@@ -528,6 +535,7 @@ __global__ void __launch_bounds__(THREADS) subalign_kernel(AlignArgs a) {
     if (threadIdx.x == 0) {
       unsigned long long off = 0;
       int st = r.status;
+      if (st == ST_STACK_OVERFLOW) st = ST_WS_DIAG_OVERFLOW;  // this kernel's small stack: the pair is retried monolithically
       if (st == ST_OK) {
         off = atomicAdd(a.arena_head, (unsigned long long)r.n_runs);
         if (off + r.n_runs > a.arena_cap) st = ST_ARENA_OVERFLOW;

@@ -176,16 +176,20 @@ struct RedSlots {
 };
 
 struct CtaShared {
-  WfMeta meta_f[MAX_SCOPE * 5];
-  WfMeta meta_r[MAX_SCOPE * 5];
-  int ub_f[MAX_SCOPE * 5];
-  int ub_r[MAX_SCOPE * 5];
+  // per-score-slot tables and the recursion stack live in a CtaTables<SLOTS, STACK> of the kernel's choosing
+  // (the one-warp kernel of split mode keeps them small to fit more CTAs per SM); bound by cta_bind()
+  WfMeta* meta_f;  // [slots * 5]
+  WfMeta* meta_r;
+  int* ub_f;       // [slots * 5]
+  int* ub_r;
+  int* ovl;        // [slots * 5] overlap search results (min k_0 per task)
+  Frame* stack;    // [stack_max]
+  int stack_max;
+  int slots_max;
   RedSlots red[2];
-  int ovl[MAX_SCOPE * 5];  // overlap search results (min k_0 per task)
   int ds[2][48];           // per direction: limits, interior bounds, row offsets, flags of the running score step
   int chunk_ctr;           // next unclaimed chunk of the running score step (dynamic balance)
   int end_val[2];          // per direction: offset of the end cell (diagonal tlen-plen, end component)
-  Frame stack[STACK_MAX];
   int sp;
   Breakpoint bp;
   int status;
@@ -203,6 +207,29 @@ struct CtaShared {
                                 // [7] backtrace, [8] overlap, [9] close phase, [10] close steps, [11..15] cells by level
 #endif
 };
+
+template <int SLOTS, int STACK>
+struct CtaTables {
+  WfMeta meta_f[SLOTS * 5];
+  WfMeta meta_r[SLOTS * 5];
+  int ub_f[SLOTS * 5];
+  int ub_r[SLOTS * 5];
+  int ovl[SLOTS * 5];
+  Frame stack[STACK];
+};
+
+// one thread; the caller synchronises before the tables are used
+template <int SLOTS, int STACK>
+WFA_FN void cta_bind(CtaShared* sh, CtaTables<SLOTS, STACK>* t) {
+  sh->meta_f = t->meta_f;
+  sh->meta_r = t->meta_r;
+  sh->ub_f = t->ub_f;
+  sh->ub_r = t->ub_r;
+  sh->ovl = t->ovl;
+  sh->stack = t->stack;
+  sh->stack_max = STACK;
+  sh->slots_max = SLOTS;
+}
 
 struct Ctx {
   CtaShared* sh;
@@ -2116,7 +2143,7 @@ WFA_FN PairResult wf_align_from(Ctx& cx, const SeqView& sv, const Frame f0, cons
     }
     cta_sync();
     if (cx.tid == 0) {
-      if (sh->sp + 2 > STACK_MAX) {
+      if (sh->sp + 2 > sh->stack_max) {
         sh->status = ST_STACK_OVERFLOW;
       } else {
         Frame h1;

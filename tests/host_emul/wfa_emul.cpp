@@ -51,6 +51,8 @@ extern "C" int emul_wfa_align(const char* pattern, int plen, const char* text, i
   std::vector<uint32_t> runs(plen + tlen + 8), bt(plen + tlen + 8);
   RunOut ro{runs.data(), (uint32_t)runs.size(), bt.data(), (uint32_t)bt.size()};
   CtaShared* sh = new CtaShared();
+  CtaTables<MAX_SCOPE, STACK_MAX>* tb_ = new CtaTables<MAX_SCOPE, STACK_MAX>();
+  cta_bind(sh, tb_);
   Ctx cx{sh, 0, 1, 0};
   PairResult r = wf_align_pair(cx, sv, plen, tlen, pen, ws, ro);
   int n = 0;
@@ -64,6 +66,7 @@ extern "C" int emul_wfa_align(const char* pattern, int plen, const char* text, i
   }
   *cigar_len = n;
   *score = r.score;
+  delete tb_;
   delete sh;
   return r.status;
 }

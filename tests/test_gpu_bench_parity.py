@@ -80,3 +80,43 @@ def test_bench_set_matches_reference(s, name):
         assert hashlib.sha1(canon.astype("<u8").tobytes()).hexdigest() == meta["partition_sha1"]
     finally:
         ctx.close()
+
+
+@pytest.mark.parametrize("split", [0, 250, 400, 700, 3000, 100000])
+def test_split_threshold_does_not_change_results(s, split):
+    """Every split threshold -- none (one CTA per pair from start to end, also the retry path), the smallest
+    allowed, and one above every score (the whole pair becomes one one-warp task) -- gives the reference's
+    records and partition on the c3 slice (reverse-complemented sequences, inversions)."""
+    from seqrush_b200 import synth
+    meta, z = load_bench_golden("c3s")
+    ids, seqs, pairs, _ = synth.bench_set("c3s")
+    sel = np.arange(0, pairs.shape[0], 5 if split in (0, 700) else 23)  # a few hundred / a few dozen pairs
+    sub = np.ascontiguousarray(pairs[sel])
+    ctx = s.Context(0)
+    try:
+        ctx.set_split(split)
+        it = s.AllPairIterator([s.AllwaveSequence(i, a.tobytes()) for i, a in zip(ids, seqs)], s.AlignmentParams(), False,
+                               False, pairs=sub, ctx=ctx)
+        k = 0
+        for rs in it._batches(True, 256):
+            for r in rs:
+                g = int(sel[k])
+                assert int(r.is_reverse) == int(z["is_reverse"][g]) and r.score == int(z["score"][g]), (split, g)
+                assert len(r.cigar_bytes) == int(z["cigar_len"][g]), (split, g)
+                assert hashlib.sha1(r.cigar_bytes).digest() == z["cigar_sha1"][g].tobytes(), (split, g)
+                k += 1
+        assert k == sel.size
+        assert ctx.stats()["failed_pairs"] == 0
+    finally:
+        ctx.close()
+
+
+def test_split_threshold_argument_checked(s):
+    ctx = s.Context(0)
+    try:
+        with pytest.raises(Exception):
+            ctx.set_split(100)
+        ctx.set_split(0)
+        ctx.set_split(250)
+    finally:
+        ctx.close()
