@@ -1558,46 +1558,68 @@ WFA_FN void wf_overlap(Ctx& cx, const Dir& d0, const Dir& d1, const Penalties& p
 #else
   const int warp = 0, nwarps = 1, lane = 0, lanes = 1;
 #endif
-  for (int task = warp; task < ntasks; task += nwarps) {
+  // The run / skip decision of a task reads a few shared-memory words and is made by one LANE per task (32 tasks per
+  // warp round); only the tasks that survive it (few: the antidiagonal bounds reject most rows) are scanned, each by
+  // the whole warp.
+  for (int tb = warp * lanes; tb < ntasks; tb += nwarps * lanes) {
+    const int task = tb + lane;
     const int i = task / 5, j = task - i * 5;
     const int c = ovl_comp_of_task(j);
     const int score_i = score_1 - i;
-    int best = INT32_MAX;
-    bool run = score_i >= 0;
+    bool run = task < ntasks && score_i >= 0;
     const int gopen = (c == C_M) ? 0 : ((c == C_I1 || c == C_D1) ? pen.o1 : pen.o2);
     if (run && score_0 + score_i - gopen >= bp_score_in) run = false;
     // h0 + h1 >= tlen  <=>  (2*h0 - k0) + (2*h1 - k1) >= plen + tlen: rows whose antidiagonal
     // bounds cannot reach that are skipped without a scan (the scan would find nothing)
     if (run && d0.st.ub[d0.st.slot(score_0) * 5 + c] + d1.st.ub[d1.st.slot(score_i) * 5 + c] < plen + tlen) run = false;
+    int max_lo = 1, min_hi = 0;
     if (run) {
       const WfMeta a = d0.st.get(score_0, c);
       const WfMeta b = d1.st.get(score_i, c);
       if (a.lo <= a.hi && b.lo <= b.hi) {
         const int lo_1 = kinv - b.hi, hi_1 = kinv - b.lo;
-        const int max_lo = imax(a.lo, lo_1), min_hi = imin(a.hi, hi_1);
-        const int32_t* r0 = d0.st.row(score_0, c);
-        const int32_t* r1 = d1.st.row(score_i, c);
-        for (int k0 = max_lo + lane; k0 <= min_hi; k0 += lanes) {
-          const int k1 = kinv - k0;
-          const int32_t h0 = r0[k0], h1 = r1[k1];
-          if (h0 + h1 >= tlen) {
-            bool ok = true;
-            if (c != C_M) {
-              // out-of-bounds guard of the indel scans (WFA/wavefront_bialign.c:534-552)
-              const int kk = breakpoint_forward ? k0 : k1;
-              const int hh = breakpoint_forward ? h0 : h1;
-              if (hh - kk > plen || hh > tlen) ok = false;
-            }
-            if (ok) {
-              best = k0;
-              break;
-            }
+        max_lo = imax(a.lo, lo_1);
+        min_hi = imin(a.hi, hi_1);
+      }
+      run = max_lo <= min_hi;
+    }
+    if (task < ntasks) cx.sh->ovl[task] = INT32_MAX;
+    uint32_t todo = warp_ballot(run);
+#if WFA_DEVICE
+    __syncwarp();
+#endif
+    while (todo) {
+      const int src = ctz32z(todo);
+      todo &= todo - 1;
+#if WFA_DEVICE
+      const int t_c = __shfl_sync(0xffffffffu, c, src), t_si = __shfl_sync(0xffffffffu, score_i, src);
+      const int t_lo = __shfl_sync(0xffffffffu, max_lo, src), t_hi = __shfl_sync(0xffffffffu, min_hi, src);
+#else
+      const int t_c = c, t_si = score_i, t_lo = max_lo, t_hi = min_hi;
+#endif
+      const int32_t* r0 = d0.st.row(score_0, t_c);
+      const int32_t* r1 = d1.st.row(t_si, t_c);
+      int best = INT32_MAX;
+      for (int k0 = t_lo + lane; k0 <= t_hi; k0 += lanes) {
+        const int k1 = kinv - k0;
+        const int32_t h0 = r0[k0], h1 = r1[k1];
+        if (h0 + h1 >= tlen) {
+          bool ok = true;
+          if (t_c != C_M) {
+            // out-of-bounds guard of the indel scans (WFA/wavefront_bialign.c:534-552)
+            const int kk = breakpoint_forward ? k0 : k1;
+            const int hh = breakpoint_forward ? h0 : h1;
+            if (hh - kk > plen || hh > tlen) ok = false;
+          }
+          if (ok) {
+            best = k0;
+            break;
           }
         }
       }
+      best = warp_min(best);
+      if (lane == 0) cx.sh->ovl[tb + src] = best;
     }
-    best = warp_min(best);
-    if (lane == 0) cx.sh->ovl[task] = best;
   }
   cta_sync();
   if (cx.tid == 0 && m0_present) {
