@@ -189,6 +189,7 @@ struct CtaShared {
   RedSlots red[2];
   int ds[2][48];           // per direction: limits, interior bounds, row offsets, flags of the running score step
   int chunk_ctr;           // next unclaimed chunk of the running score step (dynamic balance)
+  int ovl_any;             // overlap search: some task found a diagonal (else the sequential replay is skipped)
   int end_val[2];          // per direction: offset of the end cell (diagonal tlen-plen, end component)
   int sp;
   Breakpoint bp;
@@ -1544,6 +1545,7 @@ WFA_FN int ovl_comp_of_task(int j) {
 
 WFA_FN void wf_overlap(Ctx& cx, const Dir& d0, const Dir& d1, const Penalties& pen, int score_0, int score_1,
                        bool breakpoint_forward) {
+  if (cx.tid == 0) cx.sh->ovl_any = 0;
   cta_sync();
   const int scope = pen.scope;
   const int plen = d0.plen, tlen = d0.tlen;
@@ -1618,11 +1620,14 @@ WFA_FN void wf_overlap(Ctx& cx, const Dir& d0, const Dir& d1, const Penalties& p
         }
       }
       best = warp_min(best);
-      if (lane == 0) cx.sh->ovl[tb + src] = best;
+      if (lane == 0) {
+        cx.sh->ovl[tb + src] = best;
+        if (best != INT32_MAX) cx.sh->ovl_any = 1;
+      }
     }
   }
   cta_sync();
-  if (cx.tid == 0 && m0_present) {
+  if (cx.tid == 0 && m0_present && cx.sh->ovl_any) {  // without a hit the replay below changes nothing
     Breakpoint bp = cx.sh->bp;
     for (int i = 0; i < scope; ++i) {
       const int score_i = score_1 - i;
