@@ -187,7 +187,7 @@ struct CtaShared {
   int stack_max;
   int slots_max;
   RedSlots red[2];
-  int ds[2][48];           // per direction: limits, interior bounds, row offsets, flags of the running score step
+  alignas(16) int ds[2][48];  // per direction: limits, interior bounds, row offsets, flags of the running score step
   int chunk_ctr;           // next unclaimed chunk of the running score step (dynamic balance)
   int ovl_any;             // overlap search: some task found a diagonal (else the sequential replay is skipped)
   int end_val[2];          // per direction: offset of the end cell (diagonal tlen-plen, end component)
@@ -921,12 +921,36 @@ struct Span4 {  // LANE-local first/last valid diagonal of one component; reduce
 //   E barrier
 //   F publish            five lanes per direction write the metas; every thread reads the results
 // ---------------------------------------------------------------------------
+// Words of ds[dir], grouped by the place that reads them so that a chunk fetches each group with ONE 128-bit
+// shared-memory load (the words are volatile: a scalar read each was 25 loads per chunk).
 enum {
-  DS_O1 = 0, DS_O2, DS_I1, DS_I2, DS_D1, DS_D2, DS_MIS, DS_WM, DS_WI1, DS_WI2, DS_WD1, DS_WD2,
-  DS_INLO, DS_INHI, DS_LO, DS_HI, DS_LOAL, DS_NCH, DS_FLAGS, DS_META,  // DS_META .. +13: seven (lo, hi) pairs
-  DS_P0 = DS_META + 14, DS_T0, DS_REV, DS_CEND, DS_NULL, DS_OVF, DS_WIDTH, DS_SLOT5, DS_S, DS_SO1, DS_SE1, DS_SO2, DS_SE2,
-  DS_NFLAGS, DS_WORDS
+  DS_O1 = 0, DS_O2, DS_I1, DS_I2,        // copy issue: row offsets of the seven sources ...
+  DS_D1, DS_D2, DS_MIS, DS_HIP,          // ... and a copy of hi
+  DS_LO, DS_HI, DS_INLO, DS_INHI,        // chunk: limits and interior
+  DS_P0, DS_T0, DS_REV, DS_CEND,         // chunk: extension and end cell
+  DS_WI1, DS_WI2, DS_WD1, DS_WD2,        // chunk: offsets of the gap rows written
+  DS_LOAL, DS_NCH, DS_WM, DS_FLAGS,      // claim decode (two words), M row written, allocation flags
+  DS_META,                               // .. +13: seven (lo, hi) pairs, fringe chunks only (16-byte aligned: 24)
+  DS_NULL = DS_META + 14, DS_OVF, DS_WIDTH, DS_SLOT5, DS_S, DS_SO1, DS_SE1, DS_SO2, DS_SE2, DS_NFLAGS, DS_WORDS
 };
+static_assert(DS_WORDS <= 48 && (DS_META & 3) == 0, "ds[] layout");
+
+WFA_FN I4 lds4v(const volatile int* p) {  // one volatile 128-bit shared-memory read (p 16-byte aligned)
+#if WFA_DEVICE
+  I4 r;
+  asm volatile("ld.volatile.shared.v4.s32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "r"((uint32_t)__cvta_generic_to_shared(const_cast<const int*>(p))));
+  return r;
+#else
+  I4 r;
+  r.x = p[0];
+  r.y = p[1];
+  r.z = p[2];
+  r.w = p[3];
+  return r;
+#endif
+}
 
 // phase B for one direction; executed by one whole warp (lane 0 writes)
 WFA_FN void wf_setup_dir(Ctx& cx, const Dir& d, const Penalties& pen, int s, int dir, int base_adj, int lane) {
@@ -1011,6 +1035,7 @@ WFA_FN void wf_setup_dir(Ctx& cx, const Dir& d, const Penalties& pen, int s, int
   ds[DS_INHI] = in_hi;
   ds[DS_LO] = lo;
   ds[DS_HI] = hi;
+  ds[DS_HIP] = hi;
   ds[DS_LOAL] = lo_al;
   ds[DS_NCH] = (hi - lo_al) / (LANES * 4) + 1;
   ds[DS_WIDTH] = hi - lo + 1;
@@ -1145,6 +1170,7 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
   // the rows were read straight into registers: profiles/r02b_*) is covered by one chunk of compute
   // instead of being waited for. The copies in flight cost no registers.
   int n_dir = -1, n_kb = 0;
+#ifdef SRGPU_DYNAMIC_CLAIM
   auto claim_issue = [&]() -> int {  // lane 0 takes the next chunk index; the value is consumed by claim_decode
     int claim = 0;
 #if WFA_DEVICE
@@ -1154,8 +1180,18 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
 #endif
     return claim;
   };
+#else
+  // chunks are dealt round-robin to the warps: chunk costs are close to uniform, and the shared-memory atomic of a
+  // dynamic claim (with its return value) was 6.7 % of the kernel's stall samples (profiles/r03h_*)
+  int my_claim = warp;
+  auto claim_issue = [&]() -> int {
+    const int claim = my_claim;
+    my_claim += nwarps;
+    return claim;
+  };
+#endif
   auto claim_decode = [&](int claim) {
-#if WFA_DEVICE
+#if WFA_DEVICE && defined(SRGPU_DYNAMIC_CLAIM)
     claim = __shfl_sync(0xffffffffu, claim, 0);
 #endif
     if (claim >= nch_all) {
@@ -1165,7 +1201,7 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
     }
     n_dir = claim >= nch0 ? 1 : 0;
     const volatile int* sn = cx.sh->ds[n_dir];
-    const int cl = claim - (n_dir ? nch0 : 0), nchunks = sn[DS_NCH];
+    const int cl = claim - (n_dir ? nch0 : 0), nchunks = n_dir ? nch_all - nch0 : nch0;
     const int ci = cl == 0 ? 0 : (cl == 1 ? nchunks - 1 : cl - 1);
     n_kb = sn[DS_LOAL] + ci * CH;
   };
@@ -1178,12 +1214,14 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
   auto prefetch = [&](int pdir, int pkb) {
     if (pdir >= 0) {
       const volatile int* sp = cx.sh->ds[pdir];
-      const int phi = sp[DS_HI];
+      const I4 pa = lds4v(sp + DS_O1), pb = lds4v(sp + DS_D1);
+      const int offs[7] = {pa.x, pa.y, pa.z, pa.w, pb.x, pb.y, pb.z};
+      const int phi = pb.w;
       const int ks = pkb + 4 * lane;  // this lane's own four diagonals
       const bool ok0 = ks <= phi + 4;
 #pragma unroll
       for (int r = 0; r < 7; ++r) {
-        const int off = sp[DS_O1 + r];
+        const int off = offs[r];
         SR_ASSERT(!ok0 || (off + ks >= 0 && off + ks + 3 < 2 * df.st.scope * 5 * df.st.W), "row slice read inside the CTA's rings");
         SR_ASSERT(((off + ks) & 3) == 0, "16-byte aligned row slice");
         if (ok0) cp_async16(wstage + r * STAGE_ROW + 4 + 4 * lane, ring + (off + ks));
@@ -1239,10 +1277,9 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
     prefetch(n_dir, n_kb);
 #endif
     const volatile int* su = cx.sh->ds[dir];
-    const int lo = su[DS_LO], hi = su[DS_HI];
-    const int fl = su[DS_FLAGS];
-    const bool a_i1 = fl & 1, a_i2 = fl & 2, a_d1 = fl & 4, a_d2 = fl & 8;
-    const int dp0 = su[DS_P0], dt0 = su[DS_T0], drev = su[DS_REV], dcend = su[DS_CEND];
+    const I4 qa = lds4v(su + DS_LO), qb = lds4v(su + DS_P0);
+    const int lo = qa.x, hi = qa.y;
+    const int dp0 = qb.x, dt0 = qb.y, drev = qb.z, dcend = qb.w;
     int32_t ins1[4], ins2[4], del1[4], del2[4], mx[4];
     bool vm[4];
     PROF_T(tc0);
@@ -1264,13 +1301,14 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
     int32_t o1R = r_o1[4], o2R = r_o2[4], d1R = r_d1[4], d2R = r_d2[4];
     claim_decode(claim_issue());
 #endif
-    const bool interior = kb >= su[DS_INLO] && kb + CH - 1 <= su[DS_INHI];  // warp-uniform
+    const bool interior = kb >= qa.z && kb + CH - 1 <= qa.w;  // warp-uniform
     if (!interior) {
       // fringe chunk: whatever lies outside its source wavefront reads as NULL
       // (WFA/wavefront_compute.c:251-295 pads the same way)
-      const WfMeta m_o1 = {su[DS_META + 0], su[DS_META + 1]}, m_o2 = {su[DS_META + 2], su[DS_META + 3]};
-      const WfMeta m_i1 = {su[DS_META + 4], su[DS_META + 5]}, m_i2 = {su[DS_META + 6], su[DS_META + 7]};
-      const WfMeta m_d1 = {su[DS_META + 8], su[DS_META + 9]}, m_d2 = {su[DS_META + 10], su[DS_META + 11]};
+      const I4 ma = lds4v(su + DS_META), mb = lds4v(su + DS_META + 4), mc = lds4v(su + DS_META + 8);
+      const WfMeta m_o1 = {ma.x, ma.y}, m_o2 = {ma.z, ma.w};
+      const WfMeta m_i1 = {mb.x, mb.y}, m_i2 = {mb.z, mb.w};
+      const WfMeta m_d1 = {mc.x, mc.y}, m_d2 = {mc.z, mc.w};
       const WfMeta m_mis = {su[DS_META + 12], su[DS_META + 13]};
 #define MSK(v, m, kk) v = ((kk) >= (m).lo && (kk) <= (m).hi) ? v : OFFSET_NULL
       MSK(o1L, m_o1, k0 - 1);
@@ -1341,10 +1379,11 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
               "row store inside the CTA's rings");
     SR_ASSERT(!lane_act || (k0 >= -(df.st.W >> 1) && k0 + 3 < (df.st.W >> 1)), "diagonal inside the row");
     if (lane_act) {
-      st4(ring + (su[DS_WI1] + k0), ins1[0], ins1[1], ins1[2], ins1[3]);
-      st4(ring + (su[DS_WI2] + k0), ins2[0], ins2[1], ins2[2], ins2[3]);
-      st4(ring + (su[DS_WD1] + k0), del1[0], del1[1], del1[2], del1[3]);
-      st4(ring + (su[DS_WD2] + k0), del2[0], del2[1], del2[2], del2[3]);
+      const I4 qw = lds4v(su + DS_WI1);
+      st4(ring + (qw.x + k0), ins1[0], ins1[1], ins1[2], ins1[3]);
+      st4(ring + (qw.y + k0), ins2[0], ins2[1], ins2[2], ins2[3]);
+      st4(ring + (qw.z + k0), del1[0], del1[1], del1[2], del1[3]);
+      st4(ring + (qw.w + k0), del2[0], del2[1], del2[2], del2[3]);
     }
     if (warp_all(all_ok)) {
       // every cell of the chunk is in bounds in all five components (then all are allocated too)
@@ -1354,6 +1393,8 @@ WFA_FN StepOut2 wf_step_multi(Ctx& cx, Dir& df, Dir& dr, const Penalties& pen, i
       sp3.add_full(k0);
       sp4.add_full(k0);
     } else {
+      const int fl = su[DS_FLAGS];
+      const bool a_i1 = fl & 1, a_i2 = fl & 2, a_d1 = fl & 4, a_d2 = fl & 8;
       bool a0 = true, a1 = true, a2 = true, a3 = true;
       if (!interior) {
         a0 = k0 >= lo && k0 <= hi;
