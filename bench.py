@@ -469,7 +469,7 @@ def main():
         "gpu_launches": int(agg["launches"]),
         "clocks": clocks,
         # primary roofline: integer issue, 23 lane-ops per wavefront cell against 148 SMs x 4 x 32 lanes
-        "roofline": {"kernel": "align_kernel (BiWFA gap-affine-2p + backtrace)", "bound": "int_issue",
+        "roofline": {"kernel": "align_kernel -> subalign_kernel -> assemble_kernel (BiWFA gap-affine-2p split by recursion level + backtrace)", "bound": "int_issue",
                      "achieved": INT_OPS_PER_CELL * r0_cells / al_s / 1e9, "peak": int_peak / 1e9, "unit": "Gop/s",
                      "frac": INT_OPS_PER_CELL * r0_cells / al_s / int_peak,
                      "cells_per_s": r0_cells / al_s, "algorithmic_ops_per_launch": INT_OPS_PER_CELL * r0_cells / n_launch,
