@@ -80,6 +80,7 @@ struct srgpu_ctx {
   int ring_diagonals = 0;
   // sequences
   uint32_t n_seqs = 0;
+  uint64_t seq_identity = 0;  // fingerprint of the loaded set (count, lengths, head and tail bytes of every sequence)
   uint64_t total_len = 0;
   uint32_t max_len = 0;
   DevBuf<uint8_t> d_fwd, d_rcsafe;
@@ -128,6 +129,7 @@ static std::mutex g_registry_mu;
 struct srgpu_uf {
   srgpu_ctx* ctx = nullptr;
   uint64_t capacity = 0;
+  uint64_t seq_identity = 0;  // sequence set the forest was first united against (0: none yet); see check_uf
   DevBuf<uint32_t> parent;
   DevBuf<unsigned long long> counters;  // [0] ops [1] links [2] validate [3] range
   DevBuf<RegionDev> regions;
@@ -262,6 +264,7 @@ extern "C" int srgpu_set_sequences(srgpu_ctx* c, const srgpu_seqview* seqs, uint
   std::vector<uint8_t> rcsafe(n);
   uint64_t bytes = SEQ_PAD, pos = 0;
   uint32_t maxlen = 0;
+  uint64_t ident = 0xcbf29ce484222325ull ^ n;
   for (uint32_t i = 0; i < n; ++i) {
     if (seqs[i].len == 0) {  // src/seqrush.rs:311-316 panics on empty sequences
       g_err = "empty sequences are not allowed";
@@ -274,6 +277,13 @@ extern "C" int srgpu_set_sequences(srgpu_ctx* c, const srgpu_seqview* seqs, uint
     byte_off[i] = bytes;
     pos_off[i] = pos;
     len[i] = (uint32_t)seqs[i].len;
+    {
+      auto mix = [&](uint64_t v) { ident = (ident ^ v) * 0x100000001b3ull; };
+      mix(seqs[i].len);
+      const uint64_t head = std::min<uint64_t>(seqs[i].len, 64);
+      for (uint64_t j = 0; j < head; ++j) mix(seqs[i].data[j]);
+      for (uint64_t j = seqs[i].len - head; j < seqs[i].len; ++j) mix(seqs[i].data[j]);
+    }
     maxlen = std::max(maxlen, len[i]);
     bytes += (seqs[i].len + SEQ_PAD + 15) & ~(uint64_t)15;
     pos += seqs[i].len;
@@ -361,6 +371,7 @@ extern "C" int srgpu_set_sequences(srgpu_ctx* c, const srgpu_seqview* seqs, uint
   c->lbits = lbits;
   c->max_pk_words = max_pk;
   c->n_seqs = n;
+  c->seq_identity = ident ? ident : 1;
   c->total_len = pos;
   c->max_len = maxlen;
   c->h_len = len;
@@ -943,6 +954,15 @@ static int check_uf(srgpu_ctx* c, srgpu_uf* uf) {
     g_err = "union-find smaller than the sequence set";
     return SRGPU_E_RANGE;
   }
+  // A context holds ONE sequence table; a forest filled against one set and then united against another (a second
+  // set uploaded into the same context in between) would silently mix the Pos spaces of the two.
+  if (uf->seq_identity == 0) {
+    uf->seq_identity = c->seq_identity;
+  } else if (uf->seq_identity != c->seq_identity) {
+    g_err = "union-find was filled against a different sequence set than the one now loaded in this context "
+            "(srgpu_uf_clear it, or use one context per sequence set)";
+    return SRGPU_E_ARG;
+  }
   return 0;
 }
 
@@ -1130,6 +1150,7 @@ extern "C" int srgpu_uf_clear(srgpu_uf* u) {
   CK(cudaGetLastError());
   CK(cudaMemsetAsync(u->counters.p, 0, 8 * sizeof(unsigned long long), c->stream));
   CK(cudaStreamSynchronize(c->stream));
+  u->seq_identity = 0;
   return SRGPU_OK;
 }
 

@@ -553,3 +553,24 @@ def test_alignment_modes_and_aligner_trait(s, oracle):
         s.create_aligner("minimap2")
     assert s.AllwaveAligner.get_prioritized_pairs([s.AlignmentSequence("a", seqs[0]), s.AlignmentSequence("b", seqs[1])], "none", ctx=ctx) == [(0, 0), (0, 1), (1, 0), (1, 1)]
     ctx.close()
+
+
+def test_union_find_rejects_a_second_sequence_set(s):
+    """A context holds one sequence table: a forest filled against one set must not be united against another
+    that was uploaded into the same context in between (its Pos space differs); srgpu_uf_clear resets that."""
+    rng = np.random.default_rng(5)
+    def mk(n, L):
+        return [s.Sequence("s%d" % i, bytes(rng.choice(np.frombuffer(b"ACGT", dtype=np.uint8), size=L))) for i in range(n)]
+    ctx = s.Context(0)
+    try:
+        a = s.SeqRush(mk(3, 300), ctx=ctx)
+        a.align_and_unite(s.Args(min_match_length=0))
+        b = s.SeqRush(mk(3, 300), ctx=ctx)  # replaces the context's sequence table
+        b.align_and_unite(s.Args(min_match_length=0))
+        with pytest.raises(Exception, match="different sequence set"):
+            a.align_and_unite(s.Args(min_match_length=0))
+        a.union_find.clear()
+        ctx.set_sequences([q.data for q in a.sequences])
+        a.align_and_unite(s.Args(min_match_length=0))
+    finally:
+        ctx.close()
