@@ -101,11 +101,12 @@ struct srgpu_ctx {
   DevBuf<uint2> d_pairs;
   DevBuf<PairOut> d_out;
   DevBuf<uint32_t> d_arena, d_todo;
-  DevBuf<unsigned long long> d_scalars;  // [0] arena_head, [1] next_pair(uint), [2] max edit distance, [3] task_count, [4] next_task
+  DevBuf<unsigned long long> d_scalars;  // [0] arena_head, [1] next_pair(uint), [2] max edit distance, [3] task_count, [4] next_task, [5] etask_count, [6] next_task of the second pass
   // split mode: tasks (sub-problems) and the workspaces of the one-warp kernel that solves them
   int sub_ctas_per_sm = SUB_CTAS;  // one-warp CTAs per SM of subalign_kernel (SRGPU_SUB_CTAS lowers it). 1500-pair c2 slice:
                                    // 13 -> 231.6 ms, 16 -> 210.7 ms; a 96-register build at 20 -> 216.5 ms (profiles/r03a_*): the
                                    // kernel is bound by instruction fetch (profiles/r02z_*), not by warps in flight
+  int sub_two_pass = 1;  // one-warp kernel in two launches: bisect down to the base-case bound, then the leaves (SRGPU_TWO_PASS=0/1)
   int split_T = 1000;  // sub-problems whose score_remaining is at most this go to subalign_kernel (0: monolithic); SRGPU_SPLIT_T.
                        // 1500-pair slices: c2 840 ms monolithic, 728 / 740 / 766 / 831 at T = 500 / 1000 / 1900 / 3900; 100 kb 2837 -> 2756 / 2737 / 2717
                        // (profiles/r02t_*, r02u_*, r02v_*)
@@ -113,6 +114,10 @@ struct srgpu_ctx {
   DevBuf<uint32_t> d_task_pair;
   DevBuf<TaskOut> d_task_out;
   DevBuf<SplitRec> d_split;
+  DevBuf<Frame> d_tasks2;        // two-pass mode of the one-warp kernel: second-level tasks and their records
+  DevBuf<uint32_t> d_task_pair2;
+  DevBuf<TaskOut> d_task_out2;
+  DevBuf<SplitRec> d_esplit;
   DevBuf<int32_t> d_ring2, d_full2;
   DevBuf<WfMeta> d_full_meta2;
   DevBuf<uint32_t> d_runs_tmp2, d_bt_tmp2;
@@ -180,6 +185,7 @@ extern "C" int srgpu_ctx_create(int device, void* stream, srgpu_ctx** out) {
   if (const char* e = getenv("SRGPU_SPLIT_T")) c->split_T = atoi(e);
   if (const char* e = getenv("SRGPU_ORIENT_CTAS")) c->orient_ctas_per_sm = std::max(1, atoi(e));
   if (const char* e = getenv("SRGPU_SUB_CTAS")) c->sub_ctas_per_sm = std::max(1, atoi(e));
+  if (const char* e = getenv("SRGPU_TWO_PASS")) c->sub_two_pass = atoi(e) != 0;
   if (const char* e = getenv("SRGPU_STAGE_SEQS")) c->stage_seqs = atoi(e) != 0 ? 1 : 0;
   *out = c;
   return SRGPU_OK;
@@ -198,6 +204,7 @@ extern "C" void srgpu_ctx_destroy(srgpu_ctx* c) {
   c->d_len.release(); c->d_ring.release(); c->d_full.release(); c->d_orient.release(); c->d_full_meta.release();
   c->d_runs_tmp.release(); c->d_bt_tmp.release(); c->d_pairs.release(); c->d_out.release(); c->d_arena.release();
   c->d_todo.release(); c->d_scalars.release(); c->d_byteoff.release(); c->d_bytes.release(); c->d_paf_recs.release(); c->d_paf_runs.release();
+  c->d_tasks2.release(); c->d_task_pair2.release(); c->d_task_out2.release(); c->d_esplit.release();
   c->d_tasks.release(); c->d_task_pair.release(); c->d_task_out.release(); c->d_split.release(); c->d_ring2.release();
   c->d_full2.release(); c->d_full_meta2.release(); c->d_runs_tmp2.release(); c->d_bt_tmp2.release();
   for (int i = 0; i < 10; ++i) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
@@ -613,6 +620,13 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
   a.task_cap = 0;
   a.task_count = (unsigned int*)(c->d_scalars.p + 3);
   a.next_task = (unsigned int*)(c->d_scalars.p + 4);
+  a.leaf_T2 = 0;
+  a.etasks = nullptr;
+  a.etask_pair = nullptr;
+  a.etask_out = nullptr;
+  a.esplit = nullptr;
+  a.etask_cap = 0;
+  a.etask_count = (unsigned int*)(c->d_scalars.p + 5);
   // split mode: geometry of the one-warp kernel. Its ring rows must hold a sub-problem of score T: either search runs
   // to about T/2 + scope, diagonals |k| <= score.
   const int split_T = (c->split_T >= 250 && !getenv("SRGPU_NO_SPLIT") && pen.scope + 1 <= SUB_SLOTS) ? c->split_T : 0;
@@ -725,7 +739,22 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
         a.task_out = c->d_task_out.p;
         a.split = c->d_split.p + first;
         a.task_cap = (unsigned int)task_cap;
-        CK(cudaMemsetAsync(c->d_scalars.p + 3, 0, 2 * sizeof(unsigned long long), c->stream));
+        CK(cudaMemsetAsync(c->d_scalars.p + 3, 0, 4 * sizeof(unsigned long long), c->stream));
+        a.etasks = nullptr;
+        if (c->sub_two_pass) {
+          const uint64_t ecap = std::min<uint64_t>(task_cap * 4, (uint64_t)1 << 26);
+          if ((rc = c->d_tasks2.ensure(ecap)) || (rc = c->d_task_pair2.ensure(ecap)) || (rc = c->d_task_out2.ensure(ecap)) ||
+              (rc = c->d_esplit.ensure(task_cap)))
+            return rc;
+          a.leaf_T2 = 250;  // WF_BIALIGN_FALLBACK_MIN_SCORE: below it the recursion takes the base case
+          a.etasks = c->d_tasks2.p;
+          a.etask_pair = c->d_task_pair2.p;
+          a.etask_out = c->d_task_out2.p;
+          a.esplit = c->d_esplit.p;
+          a.etask_cap = (unsigned int)ecap;
+        }
+      } else {
+        a.etasks = nullptr;
       }
       CK(cudaEventRecord(c->ev[1], c->stream));
       cudaError_t e = launch_align(a, threads, ctas_per_sm, cur_grid, smem, c->stream);
@@ -743,8 +772,22 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
         s2.full_meta = c->d_full_meta2.p;
         s2.runs_tmp = c->d_runs_tmp2.p;
         s2.bt_tmp = c->d_bt_tmp2.p;
-        subalign_kernel<32, SUB_CTAS><<<sub_grid, 32, sub_smem, c->stream>>>(s2);
+        subalign_kernel<32, SUB_CTAS><<<sub_grid, 32, sub_smem, c->stream>>>(s2);  // one pass: whole tasks; two: bisection only
         CK(cudaGetLastError());
+        if (a.etasks) {
+          CK(cudaEventRecord(c->ev[8], c->stream));
+          AlignArgs s3 = s2;  // second pass: the leaves are the tasks now
+          s3.tasks = a.etasks;
+          s3.task_pair = a.etask_pair;
+          s3.task_out = a.etask_out;
+          s3.task_cap = a.etask_cap;
+          s3.task_count = a.etask_count;
+          s3.next_task = (unsigned int*)(c->d_scalars.p + 6);
+          s3.etasks = nullptr;
+          subalign_kernel<32, SUB_CTAS><<<sub_grid, 32, sub_smem, c->stream>>>(s3);
+          CK(cudaGetLastError());
+          c->stats.kernel_launches++;
+        }
         CK(cudaEventRecord(c->ev[7], c->stream));
         assemble_kernel<128><<<(unsigned)std::min<uint64_t>(cn, (uint64_t)c->n_sm * 8), 128, 0, c->stream>>>(a);
         CK(cudaGetLastError());
@@ -766,8 +809,14 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
         cudaEventElapsedTime(&m3, c->ev[7], c->ev[2]);
         unsigned int nt = 0;
         cudaMemcpy(&nt, c->d_scalars.p + 3, 4, cudaMemcpyDeviceToHost);
-        fprintf(stderr, "[srgpu] split T=%d: align_kernel %.1f ms, subalign_kernel %.1f ms (%u tasks, grid %d, W %d), assemble_kernel %.2f ms\n",
-                split_T, m1, m2, nt, sub_grid, sub_W, m3);
+        float m2a = 0;
+        unsigned int nl = 0;
+        if (a.etasks) {
+          cudaEventElapsedTime(&m2a, c->ev[6], c->ev[8]);
+          cudaMemcpy(&nl, c->d_scalars.p + 5, 4, cudaMemcpyDeviceToHost);
+        }
+        fprintf(stderr, "[srgpu] split T=%d: align_kernel %.1f ms, subalign_kernel %.1f ms (%u tasks, grid %d, W %d; bisect pass %.1f ms, %u leaves), assemble_kernel %.2f ms\n",
+                split_T, m1, m2, nt, sub_grid, sub_W, m2a, nl, m3);
       }
       if (attempt == 0) {
         CK(cudaEventElapsedTime(&ms, c->ev[4], c->ev[5]));

@@ -121,6 +121,16 @@ struct AlignArgs {
   unsigned int task_cap;
   unsigned int* task_count;     // tasks emitted so far
   unsigned int* next_task;      // subalign_kernel's work counter
+  // two-pass mode of the one-warp kernel: its first launch only bisects the tasks down to the base-case threshold
+  // and emits what is left as second-level tasks ("leaves"), its second launch finishes those. A launch of
+  // subalign_kernel emits when etasks != nullptr; assemble_kernel walks pair -> tasks -> leaves when it is set.
+  int leaf_T2;                  // threshold of the first pass (250: the reference's base-case bound)
+  struct Frame* etasks;         // [etask_cap] second-level tasks
+  uint32_t* etask_pair;         // [etask_cap]
+  struct TaskOut* etask_out;    // [etask_cap] results of the second pass
+  struct SplitRec* esplit;      // [task_cap] by first-level task: its leaves
+  unsigned int etask_cap;
+  unsigned int* etask_count;
 };
 
 struct TaskOut {
@@ -530,6 +540,41 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) subalign_kernel(AlignArgs a
     sv.t = a.seqs.pk_fwd + a.seqs.pk_off[pr.y];
     sv.lbits = a.seqs.lbits;
     const long long per_edit = max(a.pen.x, min(a.pen.o1 + a.pen.e1, a.pen.o2 + a.pen.e2));
+    if (a.etasks != nullptr) {
+      // first pass of the two-pass mode: bisect only; the run buffer holds the emitted leaves (32-byte frames)
+      Frame* leaves = reinterpret_cast<Frame*>(ro.runs);
+      const uint32_t leaf_cap = (uint32_t)(((size_t)a.runs_cap * sizeof(uint32_t)) / sizeof(Frame));
+      const PairResult rs = wf_align_from(cx, sv, f, a.pen, ws, ro, per_edit * (long long)a.out[pi].edit_distance, leaves,
+                                          leaf_cap, a.leaf_T2);
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        int st = rs.status;
+        if (st == ST_STACK_OVERFLOW) st = ST_WS_DIAG_OVERFLOW;  // this kernel's small stack: monolithic retry
+        unsigned int first = 0;
+        if (st == ST_OK) {
+          first = atomicAdd(a.etask_count, rs.n_runs);
+          if ((unsigned long long)first + rs.n_runs > a.etask_cap) st = ST_ARENA_OVERFLOW;
+        }
+        sh.bcast[3] = st;
+        sh.bcast[4] = (int)first;
+        SplitRec sr;
+        sr.cells = sh.cells;
+        sr.first_task = first;
+        sr.n_tasks = st == ST_OK ? rs.n_runs : 0;
+        sr.status = st;
+        sr.score = rs.score;
+        a.esplit[ti] = sr;
+      }
+      __syncthreads();
+      if (sh.bcast[3] == ST_OK) {
+        const unsigned int first = (unsigned int)sh.bcast[4];
+        for (uint32_t i = threadIdx.x; i < rs.n_runs; i += THREADS) {
+          a.etasks[first + i] = leaves[i];
+          a.etask_pair[first + i] = pi;
+        }
+      }
+      continue;
+    }
     const PairResult r = wf_align_from(cx, sv, f, a.pen, ws, ro, per_edit * (long long)a.out[pi].edit_distance, nullptr, 0, 0);
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -577,7 +622,7 @@ __global__ void __launch_bounds__(THREADS) assemble_kernel(AlignArgs a) {
   __shared__ unsigned int s_cnt[8];
   __shared__ unsigned long long s_off, s_cells;
   __shared__ int s_st, s_score;
-  __shared__ uint32_t s_total, s_npatch;
+  __shared__ uint32_t s_total, s_npatch, s_npieces;
   for (uint32_t slot = blockIdx.x; slot < a.n_pairs; slot += gridDim.x) {
     const uint32_t pi = a.todo ? a.todo[slot] : slot;
     const SplitRec sr = a.split[pi];
@@ -589,40 +634,63 @@ __global__ void __launch_bounds__(THREADS) assemble_kernel(AlignArgs a) {
       unsigned long long cells = sr.cells;
       uint32_t out_n = 0, npatch = 0;
       if (st == ST_OK && sr.n_tasks > (uint32_t)ASM_MAX_TASKS) st = ST_STACK_OVERFLOW;
+      s_npieces = 0;
       if (st == ST_OK) {
         bool have_last = false;
         uint32_t last_pos = 0, last_val = 0;
-        for (uint32_t t = 0; t < sr.n_tasks; ++t) {
-          const TaskOut to = a.task_out[sr.first_task + t];
-          const Frame tf = a.tasks[sr.first_task + t];
-          cells += to.cells;
-          if (to.status != ST_OK) {
-            if (st == ST_OK || to.status == ST_WS_DIAG_OVERFLOW) st = to.status;
-            continue;
+        uint32_t n_pieces = 0;  // pieces = tasks (one-pass) or leaves (two-pass), in alignment order
+        const bool two = a.etasks != nullptr;
+        for (uint32_t t = 0; t < sr.n_tasks && st == ST_OK; ++t) {
+          SplitRec lr;  // the pieces of task t
+          lr.first_task = sr.first_task + t;
+          lr.n_tasks = 1;
+          if (two) {
+            lr = a.esplit[sr.first_task + t];
+            cells += lr.cells;
+            if (lr.status != ST_OK) {
+              st = lr.status;
+              break;
+            }
+            if (a.tasks[sr.first_task + t].level == 0 && lr.score != INT32_MIN) score = lr.score;  // whole pair, bisected there
+            if (n_pieces + lr.n_tasks > (uint32_t)ASM_MAX_TASKS) {
+              st = ST_STACK_OVERFLOW;
+              break;
+            }
           }
-          if (tf.level == 0) score = to.score;  // the whole pair was one task
-          s_cnt_t[t] = 0;
-          s_dst[t] = out_n;
-          s_src[t] = to.run_off;
-          if (to.n_runs == 0) continue;
-          const uint32_t r0 = a.arena[to.run_off];
-          uint32_t skip = 0;
-          if (have_last && ((r0 ^ last_val) & 3u) == 0) {
-            last_val += (r0 >> 2) << 2;
-            skip = 1;
+          for (uint32_t l = 0; l < lr.n_tasks; ++l) {
+            const TaskOut to = two ? a.etask_out[lr.first_task + l] : a.task_out[lr.first_task + l];
+            const Frame tf = two ? a.etasks[lr.first_task + l] : a.tasks[lr.first_task + l];
+            const uint32_t x = n_pieces++;
+            cells += to.cells;
+            s_cnt_t[x] = 0;
+            s_dst[x] = out_n;
+            s_src[x] = to.run_off;
+            if (to.status != ST_OK) {
+              if (st == ST_OK || to.status == ST_WS_DIAG_OVERFLOW) st = to.status;
+              continue;
+            }
+            if (tf.level == 0) score = to.score;  // the whole pair was one piece
+            if (to.n_runs == 0) continue;
+            const uint32_t r0 = a.arena[to.run_off];
+            uint32_t skip = 0;
+            if (have_last && ((r0 ^ last_val) & 3u) == 0) {
+              last_val += (r0 >> 2) << 2;
+              skip = 1;
+            }
+            if (to.n_runs - skip == 0) continue;  // the whole piece went into the open run
+            if (have_last) {
+              s_patch_pos[npatch] = last_pos;
+              s_patch_val[npatch++] = last_val;
+            }
+            s_src[x] = to.run_off + skip;
+            s_cnt_t[x] = to.n_runs - skip;
+            out_n += to.n_runs - skip;
+            last_pos = out_n - 1;
+            last_val = a.arena[to.run_off + to.n_runs - 1];
+            have_last = true;
           }
-          if (to.n_runs - skip == 0) continue;  // the whole piece went into the open run
-          if (have_last) {
-            s_patch_pos[npatch] = last_pos;
-            s_patch_val[npatch++] = last_val;
-          }
-          s_src[t] = to.run_off + skip;
-          s_cnt_t[t] = to.n_runs - skip;
-          out_n += to.n_runs - skip;
-          last_pos = out_n - 1;
-          last_val = a.arena[to.run_off + to.n_runs - 1];
-          have_last = true;
         }
+        s_npieces = n_pieces;
         if (have_last) {
           s_patch_pos[npatch] = last_pos;
           s_patch_val[npatch++] = last_val;
@@ -644,7 +712,7 @@ __global__ void __launch_bounds__(THREADS) assemble_kernel(AlignArgs a) {
     const int st = s_st;
     const unsigned long long off = s_off;
     if (st == ST_OK) {
-      for (uint32_t t = 0; t < sr.n_tasks; ++t) {
+      for (uint32_t t = 0; t < s_npieces; ++t) {
         const uint32_t n = s_cnt_t[t], d = s_dst[t];
         const unsigned long long src = s_src[t];
         for (uint32_t i = threadIdx.x; i < n; i += THREADS) a.arena[off + d + i] = a.arena[src + i];
