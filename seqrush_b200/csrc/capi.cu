@@ -106,6 +106,7 @@ struct srgpu_ctx {
   int sub_ctas_per_sm = SUB_CTAS;  // one-warp CTAs per SM of subalign_kernel (SRGPU_SUB_CTAS lowers it). 1500-pair c2 slice:
                                    // 13 -> 231.6 ms, 16 -> 210.7 ms; a 96-register build at 20 -> 216.5 ms (profiles/r03a_*): the
                                    // kernel is bound by instruction fetch (profiles/r02z_*), not by warps in flight
+  int leaf_ctas_per_sm = LEAF_CTAS;  // SRGPU_LEAF_CTAS
   int sub_two_pass = 1;  // one-warp kernel in two launches: bisect down to the base-case bound, then the leaves (SRGPU_TWO_PASS=0/1)
   int split_T = 1000;  // sub-problems whose score_remaining is at most this go to subalign_kernel (0: monolithic); SRGPU_SPLIT_T.
                        // 1500-pair slices: c2 840 ms monolithic, 728 / 740 / 766 / 831 at T = 500 / 1000 / 1900 / 3900; 100 kb 2837 -> 2756 / 2737 / 2717
@@ -186,6 +187,7 @@ extern "C" int srgpu_ctx_create(int device, void* stream, srgpu_ctx** out) {
   if (const char* e = getenv("SRGPU_ORIENT_CTAS")) c->orient_ctas_per_sm = std::max(1, atoi(e));
   if (const char* e = getenv("SRGPU_SUB_CTAS")) c->sub_ctas_per_sm = std::max(1, atoi(e));
   if (const char* e = getenv("SRGPU_TWO_PASS")) c->sub_two_pass = atoi(e) != 0;
+  if (const char* e = getenv("SRGPU_LEAF_CTAS")) c->leaf_ctas_per_sm = std::max(1, atoi(e));
   if (const char* e = getenv("SRGPU_STAGE_SEQS")) c->stage_seqs = atoi(e) != 0 ? 1 : 0;
   *out = c;
   return SRGPU_OK;
@@ -634,12 +636,12 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
   // pair to the monolithic retry)
   int sub_W = ((int)std::min<long long>((long long)split_T + 2 * pen.scope + 128, (long long)fullW) + 63) & ~63;
   const size_t sub_smem = (size_t)STAGE_INTS * sizeof(int32_t);
-  int sub_grid = 0;
+  int sub_grid = 0, leaf_grid = 0;
   uint64_t task_cap = 0;
   if (split_T) {
     int nb = 0;
-    cudaFuncSetAttribute(subalign_kernel<32, SUB_CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sub_smem);
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, subalign_kernel<32, SUB_CTAS>, 32, sub_smem) != cudaSuccess || nb < 1) nb = 1;
+    cudaFuncSetAttribute(subalign_kernel<32, SUB_CTAS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sub_smem);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, subalign_kernel<32, SUB_CTAS, false>, 32, sub_smem) != cudaSuccess || nb < 1) nb = 1;
     sub_grid = c->n_sm * std::min(nb, c->sub_ctas_per_sm);
     {
       const size_t budget = (size_t)24 << 30, per_diag = (size_t)2 * (pen.scope + 1) * 5 * sizeof(int32_t);
@@ -648,10 +650,20 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
     }
     const size_t sub_ring = (size_t)2 * (pen.scope + 1) * 5 * sub_W;
     if ((rc = c->d_ring2.ensure((size_t)sub_grid * sub_ring))) return rc;
-    if ((rc = c->d_full2.ensure((size_t)sub_grid * 5 * cap * cap))) return rc;
-    if ((rc = c->d_full_meta2.ensure((size_t)sub_grid * cap * 5))) return rc;
-    if ((rc = c->d_runs_tmp2.ensure((size_t)sub_grid * runs_cap))) return rc;
-    if ((rc = c->d_bt_tmp2.ensure((size_t)sub_grid * runs_cap))) return rc;
+    // the leaf launch of the two-pass mode: no ring, no staging buffer, <= 64 registers: up to 32 one-warp CTAs per SM
+    // (its base cases wait on global-memory rows: long scoreboard 3.8 of 9 stall cycles per issue at 13 CTAs/SM,
+    // profiles/r03p_*), each with its own base-case store and two short run buffers
+    leaf_grid = sub_grid;
+    if (c->sub_two_pass) {
+      int nl = 0;
+      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nl, subalign_kernel<32, LEAF_CTAS, true>, 32, 0) != cudaSuccess || nl < 1) nl = 1;
+      leaf_grid = c->n_sm * std::min(nl, c->leaf_ctas_per_sm);
+    }
+    const size_t wgrid = (size_t)std::max(sub_grid, leaf_grid);
+    if ((rc = c->d_full2.ensure(wgrid * 5 * cap * cap))) return rc;
+    if ((rc = c->d_full_meta2.ensure(wgrid * cap * 5))) return rc;
+    if ((rc = c->d_runs_tmp2.ensure(std::max((size_t)sub_grid * runs_cap, (size_t)leaf_grid * LEAF_RUNS_CAP)))) return rc;
+    if ((rc = c->d_bt_tmp2.ensure(std::max((size_t)sub_grid * runs_cap, (size_t)leaf_grid * LEAF_RUNS_CAP)))) return rc;
   }
 
   CK(cudaEventRecord(c->ev[0], c->stream));
@@ -772,7 +784,7 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
         s2.full_meta = c->d_full_meta2.p;
         s2.runs_tmp = c->d_runs_tmp2.p;
         s2.bt_tmp = c->d_bt_tmp2.p;
-        subalign_kernel<32, SUB_CTAS><<<sub_grid, 32, sub_smem, c->stream>>>(s2);  // one pass: whole tasks; two: bisection only
+        subalign_kernel<32, SUB_CTAS, false><<<sub_grid, 32, sub_smem, c->stream>>>(s2);  // one pass: whole tasks; two: bisection only
         CK(cudaGetLastError());
         if (a.etasks) {
           CK(cudaEventRecord(c->ev[8], c->stream));
@@ -784,7 +796,8 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
           s3.task_count = a.etask_count;
           s3.next_task = (unsigned int*)(c->d_scalars.p + 6);
           s3.etasks = nullptr;
-          subalign_kernel<32, SUB_CTAS><<<sub_grid, 32, sub_smem, c->stream>>>(s3);
+          s3.runs_cap = LEAF_RUNS_CAP;  // a leaf's score is at most the recovery bound (500): <= 1001 runs
+          subalign_kernel<32, LEAF_CTAS, true><<<leaf_grid, 32, 0, c->stream>>>(s3);
           CK(cudaGetLastError());
           c->stats.kernel_launches++;
         }

@@ -493,11 +493,13 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
 static constexpr int SUB_SLOTS = 32;  // ring slots of the one-warp kernel (scope + 1 <= 32, else the launch stays monolithic)
 static constexpr int SUB_CTAS = 16;   // one-warp CTAs per SM (128 registers; the tables below keep shared memory at 10 KB per CTA)
 static constexpr int SUB_STACK = 32;  // a task starts below split_T: a few levels deep at most; overflow -> monolithic retry
-template <int THREADS, int MIN_CTAS>
+static constexpr unsigned int LEAF_RUNS_CAP = 8192;  // run / backtrace buffer of a leaf CTA (uint32 each)
+static constexpr int LEAF_CTAS = 32;  // one-warp CTAs per SM of the leaf launch (<= 64 registers, no staging buffer)
+template <int THREADS, int MIN_CTAS, bool LEAF>
 __global__ void __launch_bounds__(THREADS, MIN_CTAS) subalign_kernel(AlignArgs a) {
-  extern __shared__ __align__(16) uint32_t s_dyn[];  // row staging buffers of the score step
+  extern __shared__ __align__(16) uint32_t s_dyn[];  // row staging buffers of the score step (none when LEAF)
   __shared__ CtaShared sh;
-  __shared__ CtaTables<SUB_SLOTS, SUB_STACK> s_tables;
+  __shared__ CtaTables<LEAF ? 1 : SUB_SLOTS, LEAF ? 2 : SUB_STACK> s_tables;
   __shared__ unsigned int s_task;
   if (threadIdx.x == 0) cta_bind(&sh, &s_tables);
   Ctx cx;
@@ -540,7 +542,7 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) subalign_kernel(AlignArgs a
     sv.t = a.seqs.pk_fwd + a.seqs.pk_off[pr.y];
     sv.lbits = a.seqs.lbits;
     const long long per_edit = max(a.pen.x, min(a.pen.o1 + a.pen.e1, a.pen.o2 + a.pen.e2));
-    if (a.etasks != nullptr) {
+    if (!LEAF && a.etasks != nullptr) {
       // first pass of the two-pass mode: bisect only; the run buffer holds the emitted leaves (32-byte frames)
       Frame* leaves = reinterpret_cast<Frame*>(ro.runs);
       const uint32_t leaf_cap = (uint32_t)(((size_t)a.runs_cap * sizeof(uint32_t)) / sizeof(Frame));
@@ -575,7 +577,8 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) subalign_kernel(AlignArgs a
       }
       continue;
     }
-    const PairResult r = wf_align_from(cx, sv, f, a.pen, ws, ro, per_edit * (long long)a.out[pi].edit_distance, nullptr, 0, 0);
+    const PairResult r = LEAF ? wf_align_leaf(cx, sv, f, a.pen, ws, ro)
+                              : wf_align_from(cx, sv, f, a.pen, ws, ro, per_edit * (long long)a.out[pi].edit_distance, nullptr, 0, 0);
     __syncthreads();
     if (threadIdx.x == 0) {
       unsigned long long off = 0;

@@ -2244,6 +2244,51 @@ WFA_FN PairResult wf_align_from(Ctx& cx, const SeqView& sv, const Frame f0, cons
   return res;
 }
 
+// A leaf of the recursion on its own (second launch of the one-warp kernel's two-pass mode): an empty side is one
+// gap run, everything else goes through the base case -- sub-problems at or below the reference's base-case bound, and
+// those whose search reached the end within the recovery bound (WFA/wavefront_bialign.c:1083-1112 takes the base case
+// for them too). No breakpoint search: the code and the registers of this path are a fraction of wf_align_from's.
+WFA_FN PairResult wf_align_leaf(Ctx& cx, const SeqView& sv, const Frame f, const Penalties& pen, const PairWorkspace& ws,
+                                const RunOut& ro) {
+  CtaShared* sh = cx.sh;
+  PairResult res;
+  res.status = ST_OK;
+  res.score = INT32_MIN;
+  res.n_runs = 0;
+  Dir df, dr, db;
+  db.st.base = ws.full;
+  db.st.meta = ws.full_meta;
+  db.st.ub = nullptr;
+  db.st.cur_s = 0;
+  db.st.cur_slot = 0;
+  db.st.modular = 0;
+  db.st.scope = pen.scope;
+  db.st.W = 0;
+  db.st.cap = ws.cap;
+  cta_sync();
+  if (cx.tid == 0) {
+    sh->n_runs = 0;
+    sh->cells = 0;
+    sh->sp = 0;
+    sh->status = ST_OK;
+  }
+  cta_sync();
+  const int fp = f.pe - f.pb, ft = f.te - f.tb;
+  if (ft == 0) {
+    if (cx.tid == 0 && !runs_push(sh, ro, OP_D, (uint32_t)fp)) sh->status = ST_WS_RUNS_OVERFLOW;
+  } else if (fp == 0) {
+    if (cx.tid == 0 && !runs_push(sh, ro, OP_I, (uint32_t)ft)) sh->status = ST_WS_RUNS_OVERFLOW;
+  } else {
+    set_dirs(df, dr, db, sv, f);
+    const int st = wf_base(cx, db, pen, ro);
+    if (st != ST_OK && cx.tid == 0) sh->status = st;
+  }
+  cta_sync();
+  res.status = sh->status;
+  res.n_runs = sh->n_runs;
+  return res;
+}
+
 WFA_FN Frame wf_root_frame(int plen, int tlen) {
   Frame f;
   f.pb = 0;
