@@ -83,7 +83,7 @@ struct srgpu_ctx {
   uint64_t seq_identity = 0;  // fingerprint of the loaded set (count, lengths, head and tail bytes of every sequence)
   uint64_t total_len = 0;
   uint32_t max_len = 0;
-  DevBuf<uint8_t> d_fwd, d_rcsafe;
+  DevBuf<uint8_t> d_fwd, d_rcsafe, d_rcinv;
   DevBuf<uint64_t> d_byte_off, d_pos_off, d_pk_off;
   DevBuf<uint32_t> d_pk_fwd, d_pk_rc;
   int lbits = 3;              // log2(bits per packed symbol): 1, 2 or 3
@@ -115,6 +115,9 @@ struct srgpu_ctx {
   DevBuf<uint32_t> d_task_pair;
   DevBuf<TaskOut> d_task_out;
   DevBuf<SplitRec> d_split;
+  DevBuf<unsigned long long> d_mirror_keys;  // strand choice once per unordered pair: hash table (q, t) -> pair slot
+  DevBuf<uint32_t> d_mirror_vals, d_mirror_of;
+  int mirror_orient = 1;         // SRGPU_MIRROR_ORIENT=0 computes both orders
   DevBuf<Frame> d_tasks2;        // two-pass mode of the one-warp kernel: second-level tasks and their records
   DevBuf<uint32_t> d_task_pair2;
   DevBuf<TaskOut> d_task_out2;
@@ -187,6 +190,7 @@ extern "C" int srgpu_ctx_create(int device, void* stream, srgpu_ctx** out) {
   if (const char* e = getenv("SRGPU_ORIENT_CTAS")) c->orient_ctas_per_sm = std::max(1, atoi(e));
   if (const char* e = getenv("SRGPU_SUB_CTAS")) c->sub_ctas_per_sm = std::max(1, atoi(e));
   if (const char* e = getenv("SRGPU_TWO_PASS")) c->sub_two_pass = atoi(e) != 0;
+  if (const char* e = getenv("SRGPU_MIRROR_ORIENT")) c->mirror_orient = atoi(e) != 0;
   if (const char* e = getenv("SRGPU_LEAF_CTAS")) c->leaf_ctas_per_sm = std::max(1, atoi(e));
   if (const char* e = getenv("SRGPU_STAGE_SEQS")) c->stage_seqs = atoi(e) != 0 ? 1 : 0;
   *out = c;
@@ -202,7 +206,7 @@ extern "C" void srgpu_ctx_destroy(srgpu_ctx* c) {
     for (srgpu_uf* u : c->ufs) orphan_uf(u);
     c->ufs.clear();
   }
-  c->d_fwd.release(); c->d_pk_fwd.release(); c->d_pk_rc.release(); c->d_pk_off.release(); c->d_rcsafe.release(); c->d_byte_off.release(); c->d_pos_off.release();
+  c->d_fwd.release(); c->d_pk_fwd.release(); c->d_pk_rc.release(); c->d_pk_off.release(); c->d_rcsafe.release(); c->d_rcinv.release(); c->d_mirror_keys.release(); c->d_mirror_vals.release(); c->d_mirror_of.release(); c->d_byte_off.release(); c->d_pos_off.release();
   c->d_len.release(); c->d_ring.release(); c->d_full.release(); c->d_orient.release(); c->d_full_meta.release();
   c->d_runs_tmp.release(); c->d_bt_tmp.release(); c->d_pairs.release(); c->d_out.release(); c->d_arena.release();
   c->d_todo.release(); c->d_scalars.release(); c->d_byteoff.release(); c->d_bytes.release(); c->d_paf_recs.release(); c->d_paf_runs.release();
@@ -270,7 +274,7 @@ extern "C" int srgpu_set_sequences(srgpu_ctx* c, const srgpu_seqview* seqs, uint
   CK(cudaSetDevice(c->device));
   std::vector<uint64_t> byte_off(n), pos_off(n);
   std::vector<uint32_t> len(n);
-  std::vector<uint8_t> rcsafe(n);
+  std::vector<uint8_t> rcsafe(n), rcinv(n);
   uint64_t bytes = SEQ_PAD, pos = 0;
   uint32_t maxlen = 0;
   uint64_t ident = 0xcbf29ce484222325ull ^ n;
@@ -314,6 +318,12 @@ extern "C" int srgpu_set_sequences(srgpu_ctx* c, const srgpu_seqview* seqs, uint
       }
     }
     rcsafe[i] = safe;
+    uint8_t inv = 1;  // upper-case ACGTN only: allwave's reverse complement (alignment.rs:174-186) is an involution there
+    for (uint64_t j = 0; j < seqs[i].len && inv; ++j) {
+      const uint8_t ch = d[j];
+      inv = (ch == 'A' || ch == 'C' || ch == 'G' || ch == 'T' || ch == 'N') ? 1 : 0;
+    }
+    rcinv[i] = inv;
   }
   // alphabet of the forward bytes plus what allwave's reverse complement can produce; the packing
   // width is the smallest that recodes it injectively (2 bits for pure ACGT, 4 bits with N / soft
@@ -351,7 +361,7 @@ extern "C" int srgpu_set_sequences(srgpu_ctx* c, const srgpu_seqview* seqs, uint
   }
   int rc;
   if ((rc = c->d_fwd.ensure(bytes)) || (rc = c->d_byte_off.ensure(n)) || (rc = c->d_pos_off.ensure(n)) ||
-      (rc = c->d_len.ensure(n)) || (rc = c->d_rcsafe.ensure(n)) || (rc = c->d_pk_off.ensure(n)) ||
+      (rc = c->d_len.ensure(n)) || (rc = c->d_rcsafe.ensure(n)) || (rc = c->d_rcinv.ensure(n)) || (rc = c->d_pk_off.ensure(n)) ||
       (rc = c->d_pk_fwd.ensure(pk_words)) || (rc = c->d_pk_rc.ensure(pk_words))) {
     cudaFreeHost(stage);
     return rc;
@@ -364,6 +374,7 @@ extern "C" int srgpu_set_sequences(srgpu_ctx* c, const srgpu_seqview* seqs, uint
   if (e == cudaSuccess && n) e = cudaMemcpyAsync(c->d_pk_off.p, pk_off.data(), n * 8, cudaMemcpyHostToDevice, c->stream);
   if (e == cudaSuccess && n) e = cudaMemcpyAsync(c->d_len.p, len.data(), n * 4, cudaMemcpyHostToDevice, c->stream);
   if (e == cudaSuccess && n) e = cudaMemcpyAsync(c->d_rcsafe.p, rcsafe.data(), n, cudaMemcpyHostToDevice, c->stream);
+  if (e == cudaSuccess && n) e = cudaMemcpyAsync(c->d_rcinv.p, rcinv.data(), n, cudaMemcpyHostToDevice, c->stream);
   if (e == cudaSuccess && n) {
     const uint32_t per = 32u >> lbits;
     dim3 grid(std::max(1u, std::min(64u, (maxlen / per + 255) / 256)), std::min(n, 65535u));
@@ -399,6 +410,7 @@ static SeqTable seq_table(srgpu_ctx* c) {
   t.len = c->d_len.p;
   t.pos_off = c->d_pos_off.p;
   t.rc_safe = c->d_rcsafe.p;
+  t.rc_inv = c->d_rcinv.p;
   t.n = c->n_seqs;
   return t;
 }
@@ -698,6 +710,7 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
     a.out = c->d_out.p + first;
     a.n_pairs = cn;
     a.todo = nullptr;
+    a.mirror_of = nullptr;
     int curW = W;
     int cur_grid = std::min<int>(grid, (int)cn);
     CK(cudaMemsetAsync(c->d_scalars.p, 0, 2 * sizeof(unsigned long long), c->stream));
@@ -708,9 +721,35 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
         ao.smem_seq_words = smem_orient ? c->max_pk_words : 0;
         CK(cudaMemsetAsync(a.next_pair, 0, sizeof(unsigned int), c->stream));
         CK(cudaEventRecord(c->ev[4], c->stream));
+        MirrorArgs mi{};
+        if (c->mirror_orient && cn >= 2) {
+          // a pair (q, t), q > t, whose mirror (t, q) is in this launch copies the mirror's strand choice (kernels.cuh)
+          uint32_t slots = 64;
+          while (slots < 2 * cn) slots <<= 1;
+          if ((rc = c->d_mirror_keys.ensure(slots)) || (rc = c->d_mirror_vals.ensure(slots)) || (rc = c->d_mirror_of.ensure(cn))) return rc;
+          CK(cudaMemsetAsync(c->d_mirror_keys.p, 0xff, (size_t)slots * sizeof(unsigned long long), c->stream));
+          mi.pairs = a.pairs;
+          mi.n = cn;
+          mi.rc_inv = a.seqs.rc_inv;
+          mi.keys = c->d_mirror_keys.p;
+          mi.vals = c->d_mirror_vals.p;
+          mi.mask = slots - 1;
+          mi.mirror_of = c->d_mirror_of.p;
+          mi.out = a.out;
+          mirror_insert_kernel<<<grid_for(cn, 256, c->n_sm), 256, 0, c->stream>>>(mi);
+          mirror_lookup_kernel<<<grid_for(cn, 256, c->n_sm), 256, 0, c->stream>>>(mi);
+          CK(cudaGetLastError());
+          ao.mirror_of = c->d_mirror_of.p;
+          c->stats.kernel_launches += 2;
+        }
         CK(cudaFuncSetAttribute(orient_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_orient));
         orient_kernel<128><<<std::min<int>(orient_grid, (int)cn), 128, smem_orient, c->stream>>>(ao);
         CK(cudaGetLastError());
+        if (ao.mirror_of) {
+          mirror_copy_kernel<<<grid_for(cn, 256, c->n_sm), 256, 0, c->stream>>>(mi);
+          CK(cudaGetLastError());
+          c->stats.kernel_launches++;
+        }
         CK(cudaEventRecord(c->ev[5], c->stream));
         c->stats.kernel_launches++;
         if (c->ring_diagonals <= 0 && curW < fullW) {

@@ -64,6 +64,7 @@ struct SeqTable {
   const uint32_t* len;
   const uint64_t* pos_off;   // offset in the concatenated Pos space (src/seqrush.rs:1816-1818)
   const uint8_t* rc_safe;    // 1 when every byte is in ACGTacgtN: allwave RC == seqrush per-base RC
+  const uint8_t* rc_inv;     // 1 when every byte is in ACGTN: allwave RC is an involution on the sequence
   // packed copies for the aligner: 1 << lbits bits per symbol, forward and allwave reverse
   // complement (allwave/src/alignment.rs:174-186); word 0 of sequence i at pk_off[i] (16-byte
   // aligned, 4 guard words on both sides)
@@ -111,6 +112,7 @@ struct AlignArgs {
   unsigned long long* arena_head;
   unsigned int* next_pair;
   const uint32_t* todo;  // optional indirection (retry lists); nullptr = identity
+  const uint32_t* mirror_of;  // orient_kernel: pairs whose strand choice is copied from the mirrored pair (else 0xffffffff); may be null
   // split mode (leaf_T > 0): align_kernel only splits the big levels of the BiWFA recursion and emits the small
   // sub-problems as tasks; subalign_kernel solves them one warp per task, assemble_kernel joins the pieces in order
   int leaf_T;
@@ -210,6 +212,72 @@ __device__ __noinline__ void prof_print(const CtaShared& sh, long long prof_star
 #endif
 
 // ---------------------------------------------------------------------------
+// Strand choice once per UNORDERED pair. For sequences over {A,C,G,T,N} allwave's reverse complement R is an
+// involution and a bijection on the alphabet, so for the two orders of a pair
+//   ED(a, b) = ED(b, a)   and   ED(R(b), a) = ED(R(R(b)), R(a)) = ED(b, R(a)) = ED(R(a), b):
+// both edit distances of (b, a) equal those of (a, b), hence the same strand and the same minimum
+// (allwave/src/alignment.rs:148-171 compares exactly these two numbers). A pair (q, t) with q > t whose mirror
+// (t, q) is in the same launch takes the mirror's result; everything else is computed as before.
+// ---------------------------------------------------------------------------
+struct MirrorArgs {
+  const uint2* pairs;
+  uint32_t n;
+  const uint8_t* rc_inv;
+  unsigned long long* keys;  // open-addressing table, ~0 = empty
+  uint32_t* vals;
+  uint32_t mask;             // slots - 1 (power of two)
+  uint32_t* mirror_of;       // [n]
+  PairOut* out;
+};
+__device__ __forceinline__ uint32_t mirror_hash(unsigned long long key, uint32_t mask) {
+  return (uint32_t)((key * 0x9E3779B97F4A7C15ull) >> 32) & mask;
+}
+__global__ void mirror_insert_kernel(MirrorArgs m) {
+  for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < m.n; p += gridDim.x * blockDim.x) {
+    const uint2 pr = m.pairs[p];
+    m.mirror_of[p] = 0xffffffffu;
+    if (pr.x >= pr.y || !m.rc_inv[pr.x] || !m.rc_inv[pr.y]) continue;
+    const unsigned long long key = ((unsigned long long)pr.x << 32) | pr.y;
+    uint32_t h = mirror_hash(key, m.mask);
+    while (true) {
+      const unsigned long long prev = atomicCAS(&m.keys[h], ~0ull, key);
+      if (prev == ~0ull) {
+        m.vals[h] = p;
+        break;
+      }
+      if (prev == key) break;  // the same pair twice in the list: the first one serves
+      h = (h + 1) & m.mask;
+    }
+  }
+}
+__global__ void mirror_lookup_kernel(MirrorArgs m) {
+  for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < m.n; p += gridDim.x * blockDim.x) {
+    const uint2 pr = m.pairs[p];
+    if (pr.x <= pr.y || !m.rc_inv[pr.x] || !m.rc_inv[pr.y]) continue;
+    const unsigned long long key = ((unsigned long long)pr.y << 32) | pr.x;
+    uint32_t h = mirror_hash(key, m.mask);
+    while (true) {
+      const unsigned long long k = m.keys[h];
+      if (k == key) {
+        m.mirror_of[p] = m.vals[h];
+        break;
+      }
+      if (k == ~0ull) break;
+      h = (h + 1) & m.mask;
+    }
+  }
+}
+__global__ void mirror_copy_kernel(MirrorArgs m) {
+  for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < m.n; p += gridDim.x * blockDim.x) {
+    const uint32_t src = m.mirror_of[p];
+    if (src == 0xffffffffu) continue;
+    m.out[p].is_reverse = m.out[src].is_reverse;
+    m.out[p].edit_distance = m.out[src].edit_distance;
+    m.out[p].ocells = 0;
+  }
+}
+
+// ---------------------------------------------------------------------------
 // Strand choice for every pair of a launch (allwave/src/alignment.rs:24-30,148-171), one pair per
 // CTA, persistent CTAs. It runs as its own launch because it needs three staged sequences (query
 // forward, query reverse complement, target) while the aligner needs two: keeping it out of
@@ -240,6 +308,7 @@ __global__ void __launch_bounds__(THREADS) orient_kernel(AlignArgs a) {
     const unsigned int slot = s_pair;
     if (slot >= a.n_pairs) break;
     const unsigned int pi = a.todo ? a.todo[slot] : slot;
+    if (a.mirror_of && a.mirror_of[pi] != 0xffffffffu) continue;  // copied from the pair (t, q) by mirror_copy_kernel
     const uint2 pr = a.pairs[pi];
     const uint32_t plen = a.seqs.len[pr.x], tlen = a.seqs.len[pr.y];
     const uint32_t* Pf = a.seqs.pk_fwd + a.seqs.pk_off[pr.x];
