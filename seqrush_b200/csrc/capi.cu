@@ -107,6 +107,7 @@ struct srgpu_ctx {
                                    // 13 -> 231.6 ms, 16 -> 210.7 ms; a 96-register build at 20 -> 216.5 ms (profiles/r03a_*): the
                                    // kernel is bound by instruction fetch (profiles/r02z_*), not by warps in flight
   int leaf_ctas_per_sm = LEAF_CTAS;  // SRGPU_LEAF_CTAS
+  int test_task_cap = 0, test_leaf_cap = 0;  // SRGPU_TEST_TASK_CAP / SRGPU_TEST_LEAF_CAP (tests only): tiny task arrays
   int sub_two_pass = 1;  // one-warp kernel in two launches: bisect down to the base-case bound, then the leaves (SRGPU_TWO_PASS=0/1)
   int split_T = 1000;  // sub-problems whose score_remaining is at most this go to subalign_kernel (0: monolithic); SRGPU_SPLIT_T.
                        // 1500-pair slices: c2 840 ms monolithic, 728 / 740 / 766 / 831 at T = 500 / 1000 / 1900 / 3900; 100 kb 2837 -> 2756 / 2737 / 2717
@@ -190,6 +191,8 @@ extern "C" int srgpu_ctx_create(int device, void* stream, srgpu_ctx** out) {
   if (const char* e = getenv("SRGPU_ORIENT_CTAS")) c->orient_ctas_per_sm = std::max(1, atoi(e));
   if (const char* e = getenv("SRGPU_SUB_CTAS")) c->sub_ctas_per_sm = std::max(1, atoi(e));
   if (const char* e = getenv("SRGPU_TWO_PASS")) c->sub_two_pass = atoi(e) != 0;
+  if (const char* e = getenv("SRGPU_TEST_TASK_CAP")) c->test_task_cap = std::max(0, atoi(e));
+  if (const char* e = getenv("SRGPU_TEST_LEAF_CAP")) c->test_leaf_cap = std::max(0, atoi(e));
   if (const char* e = getenv("SRGPU_MIRROR_ORIENT")) c->mirror_orient = atoi(e) != 0;
   if (const char* e = getenv("SRGPU_LEAF_CTAS")) c->leaf_ctas_per_sm = std::max(1, atoi(e));
   if (const char* e = getenv("SRGPU_STAGE_SEQS")) c->stage_seqs = atoi(e) != 0 ? 1 : 0;
@@ -567,7 +570,10 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
   int grid = c->n_sm * resident;
   if ((uint64_t)grid > n_pairs) grid = (int)n_pairs;
   // workspace geometry
-  const int fullW = (int)(2 * ((uint64_t)maxlen + 4));
+  // a full row: every diagonal -plen .. tlen, one more on each side before the trim, and the 8 diagonals of slack the
+  // vector step keeps (a row of exactly 2 * (maxlen + 4) overflowed for pairs whose wavefront reaches the corner
+  // diagonals -- unrelated sequences -- whenever that number was already a multiple of 64)
+  const int fullW = (int)(2 * ((uint64_t)maxlen + 16));
   int W = c->ring_diagonals > 0 ? c->ring_diagonals : 32768;
   if (W > fullW) W = fullW;
   W = (W + 63) & ~63;
@@ -781,6 +787,7 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
       a.leaf_T = 0;
       if (split_now) {
         task_cap = std::min<uint64_t>(std::max<uint64_t>((uint64_t)cn * 256, 65536), (uint64_t)1 << 26);
+        if (c->test_task_cap > 0) task_cap = (uint64_t)c->test_task_cap;  // tests: force the overflow -> monolithic retry path
         if ((rc = c->d_tasks.ensure(task_cap)) || (rc = c->d_task_pair.ensure(task_cap)) || (rc = c->d_task_out.ensure(task_cap)) ||
             (rc = c->d_split.ensure(n_pairs)))
           return rc;
@@ -793,7 +800,8 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
         CK(cudaMemsetAsync(c->d_scalars.p + 3, 0, 4 * sizeof(unsigned long long), c->stream));
         a.etasks = nullptr;
         if (c->sub_two_pass) {
-          const uint64_t ecap = std::min<uint64_t>(task_cap * 4, (uint64_t)1 << 26);
+          uint64_t ecap = std::min<uint64_t>(task_cap * 4, (uint64_t)1 << 26);
+          if (c->test_leaf_cap > 0) ecap = (uint64_t)c->test_leaf_cap;
           if ((rc = c->d_tasks2.ensure(ecap)) || (rc = c->d_task_pair2.ensure(ecap)) || (rc = c->d_task_out2.ensure(ecap)) ||
               (rc = c->d_esplit.ensure(task_cap)))
             return rc;
@@ -885,6 +893,7 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
         const int st = h_out[i].status;
         if (st == ST_WS_DIAG_OVERFLOW) { again.push_back(i); diag = true; }
         else if (st == ST_ARENA_OVERFLOW) { again.push_back(i); arena_over = true; }
+        else if (st == ST_TASK_OVERFLOW) { again.push_back(i); }
       }
       if (again.empty()) break;
       // every retry completes the pairs that fit (the arena is reused, the ring gets its full width), so

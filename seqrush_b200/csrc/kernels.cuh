@@ -149,6 +149,7 @@ struct SplitRec {
 };
 
 static constexpr int ST_ARENA_OVERFLOW = 6;
+static constexpr int ST_TASK_OVERFLOW = 8;  // split mode: task / leaf array full -> the pair is re-run on the monolithic path
 
 // ---- bulk asynchronous copy global -> shared (TMA engine, 1-D form) completing on an mbarrier ----
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -446,7 +447,7 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
         unsigned int first = 0;
         if (st == ST_OK) {
           first = atomicAdd(a.task_count, rs.n_runs);
-          if ((unsigned long long)first + rs.n_runs > a.task_cap) st = ST_ARENA_OVERFLOW;
+          if ((unsigned long long)first + rs.n_runs > a.task_cap) st = ST_TASK_OVERFLOW;
         }
         sh.bcast[3] = st;
         sh.bcast[4] = (int)first;
@@ -459,9 +460,12 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) align_kernel(AlignArgs a) {
         a.split[pi] = sr;
       }
       __syncthreads();
-      if (sh.bcast[3] == ST_OK) {
+      if (sh.bcast[3] == ST_OK || sh.bcast[3] == ST_TASK_OVERFLOW) {
+        // (on overflow the slots this pair was given below the capacity are filled all the same: the one-warp kernel
+        // walks [0, min(count, cap)) and must find valid frames there; the pair itself is re-run monolithically)
         const unsigned int first = (unsigned int)sh.bcast[4];
-        for (uint32_t i = threadIdx.x; i < rs.n_runs; i += THREADS) {
+        const uint32_t n_fit = first < a.task_cap ? min(rs.n_runs, a.task_cap - first) : 0u;
+        for (uint32_t i = threadIdx.x; i < n_fit; i += THREADS) {
           a.tasks[first + i] = leaves[i];
           a.task_pair[first + i] = pi;
         }
@@ -624,7 +628,7 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) subalign_kernel(AlignArgs a
         unsigned int first = 0;
         if (st == ST_OK) {
           first = atomicAdd(a.etask_count, rs.n_runs);
-          if ((unsigned long long)first + rs.n_runs > a.etask_cap) st = ST_ARENA_OVERFLOW;
+          if ((unsigned long long)first + rs.n_runs > a.etask_cap) st = ST_TASK_OVERFLOW;
         }
         sh.bcast[3] = st;
         sh.bcast[4] = (int)first;
@@ -637,9 +641,10 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) subalign_kernel(AlignArgs a
         a.esplit[ti] = sr;
       }
       __syncthreads();
-      if (sh.bcast[3] == ST_OK) {
+      if (sh.bcast[3] == ST_OK || sh.bcast[3] == ST_TASK_OVERFLOW) {
         const unsigned int first = (unsigned int)sh.bcast[4];
-        for (uint32_t i = threadIdx.x; i < rs.n_runs; i += THREADS) {
+        const uint32_t n_fit = first < a.etask_cap ? min(rs.n_runs, a.etask_cap - first) : 0u;
+        for (uint32_t i = threadIdx.x; i < n_fit; i += THREADS) {
           a.etasks[first + i] = leaves[i];
           a.etask_pair[first + i] = pi;
         }

@@ -120,3 +120,36 @@ def test_split_threshold_argument_checked(s):
         ctx.set_split(250)
     finally:
         ctx.close()
+
+
+@pytest.mark.parametrize("env", [{"SRGPU_TEST_TASK_CAP": "40"}, {"SRGPU_TEST_LEAF_CAP": "200"}, {"SRGPU_TWO_PASS": "0"},
+                                 {"SRGPU_MIRROR_ORIENT": "0"}])
+def test_split_buffers_overflow_and_variants(s, env, monkeypatch):
+    """Pairs whose sub-problems do not fit the task / leaf arrays are re-run on the monolithic path (tiny arrays force
+    it for most pairs of the launch); the one-pass form of the one-warp kernel and both-orders strand choice give the
+    same records. All against the c3 slice golden."""
+    from seqrush_b200 import synth
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    meta, z = load_bench_golden("c3s")
+    ids, seqs, pairs, _ = synth.bench_set("c3s")
+    sel = np.arange(0, pairs.shape[0], 17)
+    sub = np.ascontiguousarray(pairs[sel])
+    ctx = s.Context(0)  # reads the environment
+    try:
+        it = s.AllPairIterator([s.AllwaveSequence(i, a.tobytes()) for i, a in zip(ids, seqs)], s.AlignmentParams(), False,
+                               False, pairs=sub, ctx=ctx)
+        k = 0
+        for rs in it._batches(True, 256):
+            for r in rs:
+                g = int(sel[k])
+                assert int(r.is_reverse) == int(z["is_reverse"][g]) and r.score == int(z["score"][g]), (env, g)
+                assert hashlib.sha1(r.cigar_bytes).digest() == z["cigar_sha1"][g].tobytes(), (env, g)
+                k += 1
+        assert k == sel.size
+        st = ctx.stats()
+        assert st["failed_pairs"] == 0
+        if "SRGPU_TEST_TASK_CAP" in env or "SRGPU_TEST_LEAF_CAP" in env:
+            assert st["retries"] > 0, "the tiny arrays were meant to overflow"
+    finally:
+        ctx.close()

@@ -574,3 +574,41 @@ def test_union_find_rejects_a_second_sequence_set(s):
         a.align_and_unite(s.Args(min_match_length=0))
     finally:
         ctx.close()
+
+
+def test_strand_choice_once_per_unordered_pair(s, oracle):
+    """The strand choice of (t, q) is copied from (q, t) only where that is exact -- both sequences over {A,C,G,T,N} --
+    and computed otherwise: a list with both orders, repeats and self pairs over sequences in upper case, lower case,
+    with N and with IUPAC bytes, and palindromic / reverse-complement-equal content where fwd == rev (forward wins).
+    (The set also holds UNRELATED sequences of 1500 and 1200 bases: their wavefronts reach the corner diagonals, which
+    once overflowed a full-width ring row of 2 * (1500 + 4) = 47 * 64 diagonals and failed the call.)"""
+    rng = np.random.default_rng(23)
+    acgt = np.frombuffer(b"ACGT", dtype=np.uint8)
+    comp = {65: 84, 67: 71, 71: 67, 84: 65, 78: 78}
+    def rc(a):
+        return np.array([comp[int(x)] for x in a[::-1]], dtype=np.uint8)
+    def mutate(a, rate):
+        a = a.copy()
+        idx = rng.choice(a.size, size=max(1, int(a.size * rate)), replace=False)
+        a[idx] = rng.choice(acgt, size=idx.size)
+        return a
+    base = rng.choice(acgt, size=1500)
+    half = rng.choice(acgt, size=600)
+    pal = np.concatenate([half, rc(half)])              # equal to its own reverse complement: fwd == rev against itself
+    seqs = [base, mutate(base, 0.02), rc(mutate(base, 0.03)), pal, mutate(pal, 0.01),
+            mutate(base, 0.02).tobytes().lower(),   # lower case: RC is not an involution
+            None, None]
+    withn = mutate(base, 0.02); withn[100:110] = ord("N"); seqs[6] = withn
+    iupac = mutate(base, 0.02); iupac[200] = ord("R"); iupac[900] = ord("Y"); seqs[7] = iupac
+    seqs = [np.frombuffer(x, dtype=np.uint8) if isinstance(x, bytes) else x for x in seqs]
+    n = len(seqs)
+    pairs = np.array([(i, j) for i in range(n) for j in range(n)] + [(1, 0), (0, 1), (3, 4), (4, 3), (2, 2)], dtype=np.uint32)
+    pairs = pairs[rng.permutation(pairs.shape[0])]
+    res = _align(s, [a.tobytes() for a in seqs], pairs)
+    ores, _ = oracle.run_pairs(seqs, pairs, threads=4)
+    n_rev = 0
+    for k, r in enumerate(res):
+        assert (r.query_idx, r.target_idx) == (int(pairs[k, 0]), int(pairs[k, 1]))
+        assert int(r.is_reverse) == ores[k][0] and r.score == ores[k][2] and len(r.cigar_bytes) == ores[k][3], (k, pairs[k])
+        n_rev += int(r.is_reverse)
+    assert n_rev > 0
