@@ -107,6 +107,7 @@ struct srgpu_ctx {
                                    // 13 -> 231.6 ms, 16 -> 210.7 ms; a 96-register build at 20 -> 216.5 ms (profiles/r03a_*): the
                                    // kernel is bound by instruction fetch (profiles/r02z_*), not by warps in flight
   int leaf_ctas_per_sm = LEAF_CTAS;  // SRGPU_LEAF_CTAS
+  int test_sub_w = 0;  // SRGPU_TEST_SUB_W (tests only): ring width of the one-warp kernel
   int test_task_cap = 0, test_leaf_cap = 0;  // SRGPU_TEST_TASK_CAP / SRGPU_TEST_LEAF_CAP (tests only): tiny task arrays
   int sub_two_pass = 1;  // one-warp kernel in two launches: bisect down to the base-case bound, then the leaves (SRGPU_TWO_PASS=0/1)
   int split_T = 1000;  // sub-problems whose score_remaining is at most this go to subalign_kernel (0: monolithic); SRGPU_SPLIT_T.
@@ -191,6 +192,7 @@ extern "C" int srgpu_ctx_create(int device, void* stream, srgpu_ctx** out) {
   if (const char* e = getenv("SRGPU_ORIENT_CTAS")) c->orient_ctas_per_sm = std::max(1, atoi(e));
   if (const char* e = getenv("SRGPU_SUB_CTAS")) c->sub_ctas_per_sm = std::max(1, atoi(e));
   if (const char* e = getenv("SRGPU_TWO_PASS")) c->sub_two_pass = atoi(e) != 0;
+  if (const char* e = getenv("SRGPU_TEST_SUB_W")) c->test_sub_w = std::max(0, atoi(e));
   if (const char* e = getenv("SRGPU_TEST_TASK_CAP")) c->test_task_cap = std::max(0, atoi(e));
   if (const char* e = getenv("SRGPU_TEST_LEAF_CAP")) c->test_leaf_cap = std::max(0, atoi(e));
   if (const char* e = getenv("SRGPU_MIRROR_ORIENT")) c->mirror_orient = atoi(e) != 0;
@@ -666,6 +668,7 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
       const size_t fit = budget / (per_diag * (size_t)sub_grid);
       if ((size_t)sub_W > fit) sub_W = (int)std::max<size_t>(fit & ~(size_t)63, 1024);
     }
+    if (c->test_sub_w > 0) sub_W = (c->test_sub_w + 63) & ~63;  // tests: a ring too narrow for most tasks -> monolithic retry
     const size_t sub_ring = (size_t)2 * (pen.scope + 1) * 5 * sub_W;
     if ((rc = c->d_ring2.ensure((size_t)sub_grid * sub_ring))) return rc;
     // the leaf launch of the two-pass mode: no ring, no staging buffer, <= 64 registers: up to 32 one-warp CTAs per SM

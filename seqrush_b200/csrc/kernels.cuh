@@ -658,6 +658,7 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) subalign_kernel(AlignArgs a
       unsigned long long off = 0;
       int st = r.status;
       if (st == ST_STACK_OVERFLOW) st = ST_WS_DIAG_OVERFLOW;  // this kernel's small stack: the pair is retried monolithically
+      if (LEAF && st == ST_WS_RUNS_OVERFLOW) st = ST_TASK_OVERFLOW;  // the leaf launch's short run buffers: same
       if (st == ST_OK) {
         off = atomicAdd(a.arena_head, (unsigned long long)r.n_runs);
         if (off + r.n_runs > a.arena_cap) st = ST_ARENA_OVERFLOW;
