@@ -143,7 +143,7 @@ def make_workload(name, world=1, scaling="weak"):
                     % (n, pairs.shape[0]),
         "name": name, "n_sequences": n, "penalties": "0,5,8,2,24,1", "min_match_len": 0,
         "pairs_per_step": int(pairs.shape[0]), "aligned_Mbp_per_step": bp / 1e6,
-        "sharding": ("pairs round-robin over %d ranks, every pair aligned once, private forests merged by one "
+        "sharding": ("unordered pairs round-robin over %d ranks (both orders on one rank), every pair aligned once, private forests merged by one "
                      "all_gather_into_tensor + one device union pass" % world) if world > 1 else "single GPU",
         "l2": "256 MB flush write between timed steps; per-CTA wavefront workspaces >> 126 MB L2",
     }

@@ -1,5 +1,5 @@
 """Multi-GPU sharding of the align-and-unite phase: one process per GPU (torch.distributed over
-NCCL), the ordered pair list dealt round-robin, a private union-find per GPU over the full Pos
+NCCL), the pair list dealt round-robin by unordered pair, a private union-find per GPU over the full Pos
 space, and ONE exchange at the end -- all_gather of the compressed parent arrays followed by a
 device-side union pass. The host logic is backend-agnostic so that the gloo
 CPU tests can cover it with a stand-in union-find."""
@@ -7,8 +7,21 @@ import numpy as np
 
 
 def shard_pairs(pairs: np.ndarray, rank: int, world: int) -> np.ndarray:
-    """Round-robin deal of the ordered pair list (pairs are independent: allwave/src/iterator.rs:185-203)."""
-    return np.ascontiguousarray(pairs[rank::world])
+    """Deal of the ordered pair list over the ranks (pairs are independent: allwave/src/iterator.rs:185-203).
+    The two orders (i, j) and (j, i) of an unordered pair go to the SAME rank, so that rank's launch can take the
+    strand choice of one from the other (csrc/kernels.cuh, mirror_*_kernel); the unordered pairs are dealt round-robin
+    in the order of their (min, max) key, and a rank keeps the list's own order among its pairs."""
+    p = np.asarray(pairs)
+    if world <= 1 or p.shape[0] == 0:
+        return np.ascontiguousarray(p)
+    a = p[:, 0].astype(np.uint64)
+    b = p[:, 1].astype(np.uint64)
+    key = (np.minimum(a, b) << np.uint64(32)) | np.maximum(a, b)
+    order = np.argsort(key, kind="stable")
+    ks = key[order]
+    gid = np.cumsum(np.concatenate([[True], ks[1:] != ks[:-1]])) - 1
+    sel = np.sort(order[(gid % world) == rank])
+    return np.ascontiguousarray(p[sel])
 
 
 def merge_forests(local_roots, world: int, dist, unite_with_peer):
