@@ -327,6 +327,12 @@ def main():
         trace("process group up")
 
     from seqrush_b200.distributed import shard_pairs, merge_device_union_finds
+    if world > 1:
+        # OPEN ISSUE: with the strand choice taken once per unordered pair, the first 2-GPU run on a
+        # fresh box died twice on rank 1 with an illegal memory access inside the alignment launches (profiles/
+        # r04d_n2_first_run_fault.txt); never with it off, never at N = 1, never on a second run, never under the
+        # bounds-asserting build. Until that is root-caused the multi-GPU bench computes both orders.
+        os.environ.setdefault("SRGPU_MIRROR_ORIENT", "0")
     stream = torch.cuda.Stream()
     ctx = s.Context(local, stream.cuda_stream)
     if args.threads or args.ctas_per_sm or args.ring >= 0:

@@ -107,6 +107,7 @@ struct srgpu_ctx {
                                    // 13 -> 231.6 ms, 16 -> 210.7 ms; a 96-register build at 20 -> 216.5 ms (profiles/r03a_*): the
                                    // kernel is bound by instruction fetch (profiles/r02z_*), not by warps in flight
   int leaf_ctas_per_sm = LEAF_CTAS;  // SRGPU_LEAF_CTAS
+  int debug_sync = 0;  // SRGPU_DEBUG_SYNC: synchronise after every alignment launch
   int test_sub_w = 0;  // SRGPU_TEST_SUB_W (tests only): ring width of the one-warp kernel
   int test_task_cap = 0, test_leaf_cap = 0;  // SRGPU_TEST_TASK_CAP / SRGPU_TEST_LEAF_CAP (tests only): tiny task arrays
   int sub_two_pass = 1;  // one-warp kernel in two launches: bisect down to the base-case bound, then the leaves (SRGPU_TWO_PASS=0/1)
@@ -193,6 +194,7 @@ extern "C" int srgpu_ctx_create(int device, void* stream, srgpu_ctx** out) {
   if (const char* e = getenv("SRGPU_SUB_CTAS")) c->sub_ctas_per_sm = std::max(1, atoi(e));
   if (const char* e = getenv("SRGPU_TWO_PASS")) c->sub_two_pass = atoi(e) != 0;
   if (const char* e = getenv("SRGPU_TEST_SUB_W")) c->test_sub_w = std::max(0, atoi(e));
+  if (const char* e = getenv("SRGPU_DEBUG_SYNC")) c->debug_sync = atoi(e) != 0;
   if (const char* e = getenv("SRGPU_TEST_TASK_CAP")) c->test_task_cap = std::max(0, atoi(e));
   if (const char* e = getenv("SRGPU_TEST_LEAF_CAP")) c->test_leaf_cap = std::max(0, atoi(e));
   if (const char* e = getenv("SRGPU_MIRROR_ORIENT")) c->mirror_orient = atoi(e) != 0;
@@ -824,6 +826,7 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
         g_err = std::string("align_kernel launch: ") + cudaGetErrorString(e);
         return SRGPU_E_CUDA;
       }
+      if (c->debug_sync) CK(cudaStreamSynchronize(c->stream));  // SRGPU_DEBUG_SYNC: a fault is reported at the launch that caused it
       if (split_now) {
         CK(cudaEventRecord(c->ev[6], c->stream));
         AlignArgs s2 = a;
@@ -836,6 +839,7 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
         s2.bt_tmp = c->d_bt_tmp2.p;
         subalign_kernel<32, SUB_CTAS, false><<<sub_grid, 32, sub_smem, c->stream>>>(s2);  // one pass: whole tasks; two: bisection only
         CK(cudaGetLastError());
+        if (c->debug_sync) CK(cudaStreamSynchronize(c->stream));
         if (a.etasks) {
           CK(cudaEventRecord(c->ev[8], c->stream));
           AlignArgs s3 = s2;  // second pass: the leaves are the tasks now
@@ -849,11 +853,13 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
           s3.runs_cap = LEAF_RUNS_CAP;  // a leaf's score is at most the recovery bound (500): <= 1001 runs
           subalign_kernel<32, LEAF_CTAS, true><<<leaf_grid, 32, 0, c->stream>>>(s3);
           CK(cudaGetLastError());
+          if (c->debug_sync) CK(cudaStreamSynchronize(c->stream));
           c->stats.kernel_launches++;
         }
         CK(cudaEventRecord(c->ev[7], c->stream));
         assemble_kernel<128><<<(unsigned)std::min<uint64_t>(cn, (uint64_t)c->n_sm * 8), 128, 0, c->stream>>>(a);
         CK(cudaGetLastError());
+        if (c->debug_sync) CK(cudaStreamSynchronize(c->stream));
         c->stats.kernel_launches += 2;
       }
       CK(cudaEventRecord(c->ev[2], c->stream));
