@@ -20,7 +20,15 @@ def shard_pairs(pairs: np.ndarray, rank: int, world: int) -> np.ndarray:
     order = np.argsort(key, kind="stable")
     ks = key[order]
     gid = np.cumsum(np.concatenate([[True], ks[1:] != ks[:-1]])) - 1
-    sel = np.sort(order[(gid % world) == rank])
+    # unordered pairs present in both orders (or repeated) are dealt round-robin among themselves, the single ones
+    # after them, so that the ranks' PAIR counts stay within one unordered pair of each other
+    size = np.bincount(gid)
+    multi = size > 1
+    owner = np.empty(size.shape[0], dtype=np.int64)
+    n_multi = int(multi.sum())
+    owner[multi] = np.arange(n_multi) % world
+    owner[~multi] = (n_multi + np.arange(size.shape[0] - n_multi)) % world
+    sel = np.sort(order[owner[gid] == rank])
     return np.ascontiguousarray(p[sel])
 
 

@@ -120,3 +120,31 @@ def test_parse_paf_line():
     assert parse_paf_line("q\t25\t0\t25\t+\tt\t30\t0\t25\t25\t25\t60\n")[-1] == ""  # no CIGAR tag
     with pytest.raises(ValueError):
         parse_paf_line("q\tx\t0\t25\t+\tt\t30\t0\t25\t25\t25\t60\n")
+
+
+def test_shard_pairs_keeps_both_orders_on_one_rank():
+    """seqrush_b200.distributed.shard_pairs: a partition of the list, both orders of an unordered pair on the same rank,
+    the list's own order kept inside a rank, sizes within one unordered pair of each other."""
+    import numpy as np
+    from seqrush_b200.distributed import shard_pairs
+    from seqrush_b200 import synth
+    pairs = synth.all_pairs(37)
+    rng = np.random.default_rng(3)
+    pairs = np.ascontiguousarray(pairs[np.sort(rng.choice(pairs.shape[0], size=900, replace=False))])  # a sparsified list
+    for world in (1, 2, 3, 8):
+        seen, sizes = set(), []
+        everything = set(map(tuple, pairs.tolist()))
+        for rank in range(world):
+            mine = shard_pairs(pairs, rank, world)
+            got = list(map(tuple, mine.tolist()))
+            assert got == [p for p in map(tuple, pairs.tolist()) if p in set(got)]  # order of the list
+            st = set(got)
+            assert not (st & seen)
+            for (a, b) in st:
+                if (b, a) in everything:
+                    assert (b, a) in st
+            seen |= st
+            sizes.append(len(got))
+        assert seen == everything
+        assert max(sizes) - min(sizes) <= 3
+    assert shard_pairs(pairs[:0], 0, 4).shape[0] == 0
