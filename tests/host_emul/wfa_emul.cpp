@@ -71,6 +71,81 @@ extern "C" int emul_wfa_align(const char* pattern, int plen, const char* text, i
   return r.status;
 }
 
+// The split path of the device (align_kernel -> subalign_kernel bisect launch -> leaf launch -> assemble_kernel) with the
+// same core functions: the pair is bisected down to `split_T`, every emitted task down to `leaf_T2`, every leaf goes
+// through wf_align_leaf, and the pieces are joined in order (a piece whose first run continues the open run is merged
+// into it). Small tables (32 ring slots, 32 stack frames) and a narrow ring for the tasks, like the one-warp kernel.
+extern "C" int emul_wfa_align_split(const char* pattern, int plen, const char* text, int tlen, int x, int o1, int e1, int o2,
+                                    int e2, int W, int cap, int lbits, int split_T, int leaf_T2, char* cigar_out,
+                                    int* cigar_len, int* score, int* n_tasks_out, int* n_leaves_out) {
+  Penalties pen{x, o1, e1, o2, e2, 0};
+  int sc = o1 + e1 > o2 + e2 ? o1 + e1 : o2 + e2;
+  if (x > sc) sc = x;
+  pen.scope = sc + 1;
+  Packer pk;
+  pk.see(pattern, plen);
+  pk.see(text, tlen);
+  if (lbits <= 0 || lbits < pk.min_lbits()) lbits = pk.min_lbits();
+  std::vector<uint32_t> pb = pk.pack(pattern, plen, lbits), tb = pk.pack(text, tlen, lbits);
+  SeqView sv{pb.data() + 4, tb.data() + 4, lbits};
+  std::vector<int32_t> rf((size_t)(pen.scope + 1) * 5 * W), rr((size_t)(pen.scope + 1) * 5 * W), full((size_t)5 * cap * cap);
+  std::vector<WfMeta> fm((size_t)cap * 5);
+  PairWorkspace ws{rf.data(), rr.data(), W, full.data(), fm.data(), cap};
+  const int subW = ((split_T + 2 * pen.scope + 128) + 63) & ~63;
+  std::vector<int32_t> sf((size_t)(pen.scope + 1) * 5 * subW), sr((size_t)(pen.scope + 1) * 5 * subW);
+  PairWorkspace ws2{sf.data(), sr.data(), subW, full.data(), fm.data(), cap};
+  std::vector<uint32_t> runs(plen + tlen + 64), bt(plen + tlen + 64);
+  RunOut ro{runs.data(), (uint32_t)runs.size(), bt.data(), (uint32_t)bt.size()};
+  CtaShared* sh = new CtaShared();
+  CtaTables<MAX_SCOPE, STACK_MAX>* big = new CtaTables<MAX_SCOPE, STACK_MAX>();
+  CtaTables<32, 32>* small = new CtaTables<32, 32>();
+  Ctx cx{sh, 0, 1, 0};
+  int status = ST_OK, sc_out = INT32_MIN;
+  std::vector<Frame> tasks, leaves;
+  {
+    cta_bind(sh, big);
+    Frame* buf = reinterpret_cast<Frame*>(runs.data());
+    const uint32_t cap_f = (uint32_t)(runs.size() * sizeof(uint32_t) / sizeof(Frame));
+    PairResult r = wf_align_from(cx, sv, wf_root_frame(plen, tlen), pen, ws, ro, (long long)1 << 40, buf, cap_f, split_T);
+    status = r.status;
+    sc_out = r.score;
+    if (status == ST_OK) tasks.assign(buf, buf + r.n_runs);
+  }
+  cta_bind(sh, small);
+  for (size_t t = 0; t < tasks.size() && status == ST_OK; ++t) {
+    Frame* buf = reinterpret_cast<Frame*>(runs.data());
+    const uint32_t cap_f = (uint32_t)(runs.size() * sizeof(uint32_t) / sizeof(Frame));
+    PairResult r = wf_align_from(cx, sv, tasks[t], pen, ws2, ro, (long long)1 << 40, buf, cap_f, leaf_T2);
+    status = r.status;
+    if (tasks[t].level == 0 && r.score != INT32_MIN) sc_out = r.score;
+    if (status == ST_OK) leaves.insert(leaves.end(), buf, buf + r.n_runs);
+  }
+  std::vector<uint32_t> joined;
+  for (size_t l = 0; l < leaves.size() && status == ST_OK; ++l) {
+    PairResult r = wf_align_leaf(cx, sv, leaves[l], pen, ws2, ro);
+    status = r.status;
+    for (uint32_t i = 0; i < r.n_runs && status == ST_OK; ++i) {
+      if (!joined.empty() && ((joined.back() ^ runs[i]) & 3u) == 0) joined.back() += (runs[i] >> 2) << 2;
+      else joined.push_back(runs[i]);
+    }
+  }
+  int n = 0;
+  const char ops[4] = {'M', 'X', 'I', 'D'};
+  if (status == ST_OK)
+    for (uint32_t v : joined) {
+      memset(cigar_out + n, ops[v & 3], v >> 2);
+      n += (int)(v >> 2);
+    }
+  *cigar_len = n;
+  *score = sc_out;
+  *n_tasks_out = (int)tasks.size();
+  *n_leaves_out = (int)leaves.size();
+  delete small;
+  delete big;
+  delete sh;
+  return status;
+}
+
 #include "../../seqrush_b200/csrc/orient_core.cuh"
 extern "C" int emul_orient(const char* pf, const char* pr, int plen, const char* text, int tlen, int lbits, int* dist) {
   Packer pk;

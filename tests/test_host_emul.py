@@ -60,3 +60,49 @@ def test_emul_narrow_ring_reports_overflow(emul):
     b = bytes(np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, 3000)])
     st, _, _ = _align(emul, a, b, (5, 8, 2, 24, 1), W=256)
     assert st == 2  # ST_WS_DIAG_OVERFLOW: the host retries with a wider ring, never a wrong answer
+
+
+def test_emul_split_path_equals_monolithic(emul):
+    """The device's split path -- bisect down to split_T, bisect every task down to the base-case bound, finish every
+    leaf with wf_align_leaf, join the pieces in order -- gives the monolithic path's CIGAR and score (same core
+    functions, host build; small tables and a narrow ring for the tasks like the one-warp kernel)."""
+    import numpy as np
+    emul.emul_wfa_align_split.argtypes = [C.c_char_p, C.c_int, C.c_char_p, C.c_int] + [C.c_int] * 10 + \
+        [C.c_char_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    rng = np.random.default_rng(77)
+    acgt = np.frombuffer(b"ACGT", dtype=np.uint8)
+
+    def mutate(a, rate):
+        out = []
+        for ch in a:
+            r = rng.random()
+            if r < rate / 3:
+                out.append(int(rng.choice(acgt)))
+            elif r < 2 * rate / 3:
+                continue
+            elif r < rate:
+                out.append(int(ch))
+                out.extend(int(x) for x in rng.choice(acgt, size=1 + (int(rng.integers(40)) if rng.random() < 0.1 else 0)))
+            else:
+                out.append(int(ch))
+        return bytes(out)
+
+    pen = (5, 8, 2, 24, 1)
+    cases = [(9000, 0.03, 1000), (7000, 0.05, 1000), (6000, 0.04, 400), (5000, 0.02, 250), (800, 0.02, 1000), (3000, 0.10, 600)]
+    deep = 0
+    for L, rate, split_T in cases:
+        a = bytes(rng.choice(acgt, size=L))
+        b = mutate(a, rate)
+        st0, sc0, cig0 = _align(emul, a, b, pen)
+        assert st0 == 0
+        W = (2 * (max(len(a), len(b)) + 16) + 63) & ~63
+        buf = C.create_string_buffer(len(a) + len(b) + 64)
+        n, sc, nt, nl = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        st = emul.emul_wfa_align_split(a, len(a), b, len(b), *pen, W, 520, 0, split_T, 250, buf, C.byref(n), C.byref(sc),
+                                       C.byref(nt), C.byref(nl))
+        assert st == 0, (L, rate, split_T, st)
+        assert buf.raw[:n.value] == cig0, (L, rate, split_T)
+        assert sc.value == sc0, (L, rate, split_T, sc.value, sc0)
+        assert nl.value >= nt.value >= 1
+        deep += int(nt.value > 1 and nl.value > nt.value)
+    assert deep >= 3, "the cases were meant to exercise both levels of the split"
