@@ -109,6 +109,7 @@ struct srgpu_ctx {
   int leaf_ctas_per_sm = LEAF_CTAS;  // SRGPU_LEAF_CTAS
   int debug_sync = 0;  // SRGPU_DEBUG_SYNC: synchronise after every alignment launch
   int test_sub_w = 0;  // SRGPU_TEST_SUB_W (tests only): ring width of the one-warp kernel
+  int test_asm_max = 0;  // SRGPU_TEST_ASM_MAX (tests only): pieces per pair the join kernel accepts
   int test_task_cap = 0, test_leaf_cap = 0;  // SRGPU_TEST_TASK_CAP / SRGPU_TEST_LEAF_CAP (tests only): tiny task arrays
   int sub_two_pass = 1;  // one-warp kernel in two launches: bisect down to the base-case bound, then the leaves (SRGPU_TWO_PASS=0/1)
   int split_T = 1000;  // sub-problems whose score_remaining is at most this go to subalign_kernel (0: monolithic); SRGPU_SPLIT_T.
@@ -195,6 +196,7 @@ extern "C" int srgpu_ctx_create(int device, void* stream, srgpu_ctx** out) {
   if (const char* e = getenv("SRGPU_TWO_PASS")) c->sub_two_pass = atoi(e) != 0;
   if (const char* e = getenv("SRGPU_TEST_SUB_W")) c->test_sub_w = std::max(0, atoi(e));
   if (const char* e = getenv("SRGPU_DEBUG_SYNC")) c->debug_sync = atoi(e) != 0;
+  if (const char* e = getenv("SRGPU_TEST_ASM_MAX")) c->test_asm_max = std::max(0, atoi(e));
   if (const char* e = getenv("SRGPU_TEST_TASK_CAP")) c->test_task_cap = std::max(0, atoi(e));
   if (const char* e = getenv("SRGPU_TEST_LEAF_CAP")) c->test_leaf_cap = std::max(0, atoi(e));
   if (const char* e = getenv("SRGPU_MIRROR_ORIENT")) c->mirror_orient = atoi(e) != 0;
@@ -651,6 +653,7 @@ static int run_pairs(srgpu_ctx* c, srgpu_uf* uf, const uint2* d_pairs, uint64_t 
   a.esplit = nullptr;
   a.etask_cap = 0;
   a.etask_count = (unsigned int*)(c->d_scalars.p + 5);
+  a.asm_max = c->test_asm_max > 0 ? (unsigned int)std::min(c->test_asm_max, ASM_MAX_TASKS) : (unsigned int)ASM_MAX_TASKS;
   // split mode: geometry of the one-warp kernel. Its ring rows must hold a sub-problem of score T: either search runs
   // to about T/2 + scope, diagonals |k| <= score.
   const int split_T = (c->split_T >= 250 && !getenv("SRGPU_NO_SPLIT") && pen.scope + 1 <= SUB_SLOTS) ? c->split_T : 0;

@@ -133,6 +133,7 @@ struct AlignArgs {
   struct SplitRec* esplit;      // [task_cap] by first-level task: its leaves
   unsigned int etask_cap;
   unsigned int* etask_count;
+  unsigned int asm_max;         // pieces assemble_kernel joins per pair (<= ASM_MAX_TASKS; tests lower it)
 };
 
 struct TaskOut {
@@ -711,7 +712,7 @@ __global__ void __launch_bounds__(THREADS) assemble_kernel(AlignArgs a) {
       int score = sr.score;
       unsigned long long cells = sr.cells;
       uint32_t out_n = 0, npatch = 0;
-      if (st == ST_OK && sr.n_tasks > (uint32_t)ASM_MAX_TASKS) st = ST_STACK_OVERFLOW;
+      if (st == ST_OK && sr.n_tasks > a.asm_max) st = ST_TASK_OVERFLOW;  // more pieces than this kernel joins: monolithic retry
       s_npieces = 0;
       if (st == ST_OK) {
         bool have_last = false;
@@ -730,8 +731,8 @@ __global__ void __launch_bounds__(THREADS) assemble_kernel(AlignArgs a) {
               break;
             }
             if (a.tasks[sr.first_task + t].level == 0 && lr.score != INT32_MIN) score = lr.score;  // whole pair, bisected there
-            if (n_pieces + lr.n_tasks > (uint32_t)ASM_MAX_TASKS) {
-              st = ST_STACK_OVERFLOW;
+            if (n_pieces + lr.n_tasks > a.asm_max) {
+              st = ST_TASK_OVERFLOW;  // (long, divergent pairs: > 1024 leaves) the pair is re-run monolithically
               break;
             }
           }

@@ -612,3 +612,4 @@ def test_strand_choice_once_per_unordered_pair(s, oracle):
         assert int(r.is_reverse) == ores[k][0] and r.score == ores[k][2] and len(r.cigar_bytes) == ores[k][3], (k, pairs[k])
         n_rev += int(r.is_reverse)
     assert n_rev > 0
+
